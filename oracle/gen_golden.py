@@ -1,0 +1,154 @@
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference in the build container.
+
+    python oracle/gen_golden.py            # needs /root/reference (or $CALIB_REFERENCE_DIR)
+
+Every file stores its inputs next to the reference's outputs so the GPU box (which has no
+reference checkout) can replay them.  Library versions are recorded in each file.
+"""
+import contextlib
+import importlib
+import io
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import ref_shim  # noqa: E402
+
+scene_mod = importlib.import_module("extrinsic-camera-calibration-from-a-moving-person_b200.scene")
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def versions():
+    import cv2
+    import scipy
+    return dict(numpy=np.__version__, scipy=scipy.__version__, cv2=cv2.__version__)
+
+
+def quiet():
+    return contextlib.redirect_stdout(io.StringIO())
+
+
+def gen_ba(name, scene_kw, available_joints, lam1, lam2, run_main=False):
+    rb, _, ru = ref_shim.load()
+    from scipy.optimize import least_squares
+    from scipy.optimize._numdiff import approx_derivative
+    sc = scene_mod.make_scene(**scene_kw)
+    sp2d, ss2d, sp3d, ss3d = scene_mod.ba_inputs(sc, available_joints)
+    C, N, J = ss2d.shape
+    x0 = ru.triangulate_with_conf(sp2d, ss2d, sc.K, sc.R_init, sc.t_init, ss2d > 0)
+    theta0 = rb.to_theta(sc.R_init, sc.t_init, x0.reshape(-1, 3))
+    args = (sc.K, sp2d.reshape(C, N * J, 2), ss2d, sp3d, ss3d, ru.OP_BONE, C, N, J, lam1, lam2)
+    f0 = rb.objfun(theta0, *args)
+    # a second evaluation point away from the triangulated start (rvec_0 forced to exactly 0:
+    # linear_*/ransac_*.json carry R_0 = I)
+    rng = np.random.default_rng(123)
+    theta1 = theta0 + rng.normal(0, 0.01, theta0.shape)
+    theta1[0:3] = 0.0
+    f1 = rb.objfun(theta1, *args)
+    J_fd = approx_derivative(lambda th: rb.objfun(th, *args), theta1, method="3-point", abs_step=1e-6)
+    out = dict(K=sc.K, R_init=sc.R_init, t_init=sc.t_init, sp2d=sp2d, ss2d=ss2d, sp3d=sp3d, ss3d=ss3d,
+               lam1=lam1, lam2=lam2, x0=x0, theta0=theta0, f0=f0, theta1=theta1, f1=f1, J_fd=J_fd,
+               versions=str(versions()))
+    if run_main:
+        with quiet():
+            R, t, x = rb.ba_main(sc.camid, sc.K, sc.R_init, sc.t_init, sp2d, ss2d, sp3d, ss3d, lam1, lam2)
+        out.update(R_lit=R, t_lit=t, x_lit=x)
+        # the reference objective driven to convergence (same objfun, same solver, tight tolerances)
+        for tag, jac in (("tight2", "2-point"), ("tight3", "3-point")):
+            res = least_squares(rb.objfun, theta0, method="trf", jac=jac, ftol=1e-14, xtol=1e-14,
+                                gtol=1e-14, max_nfev=300, args=args)
+            R, t, x = rb.from_theta(res.x, C)
+            out.update({f"R_{tag}": R, f"t_{tag}": t, f"cost_{tag}": res.cost, f"nfev_{tag}": res.nfev})
+    np.savez_compressed(os.path.join(OUT, f"ba_{name}.npz"), **out)
+    print("wrote", name, "m =", f0.size, "n =", theta0.size)
+
+
+def gen_ransac(name, scene_kw, n_iter, seed, th_2d, th_3d_deg):
+    _, rc, ru = ref_shim.load()
+    sc = scene_mod.make_scene(**scene_kw)
+    C = sc.C
+    mask = (sc.s2d > 0) * (sc.s3d == 1)
+    vis = ru.visible_from_all_cam(mask)
+    vc = ru.joints2orientations(sc.p3d, vis, ru.OP_BONE)
+    y = ru.joints2projections(np.copy(sc.p2d), vis, ru.OP_KEY_SUB)
+    n = np.ones((C, y.shape[1], 3))
+    n[:, :, :2] = y
+    n = np.array([n[i] @ np.linalg.inv(sc.K[i]).T for i in range(C)])
+    th_3d = th_3d_deg / 180 * np.pi
+    N, M = vc.shape[1], n.shape[1]
+
+    # literal per-hypothesis pass: the reference's own calib_linear + triangulate, scored as at
+    # calib_ransac.py:154-180
+    rng = np.random.default_rng(seed)
+    scores, Rs, ts, sn, sm = [], [], [], [], []
+    for it in range(n_iter):
+        a = rng.choice(N, size=10, replace=False)
+        b = rng.choice(M, size=10, replace=False)
+        R, t, _ = rc.calib_linear(vc[:, a, :], n[:, b, :])
+        P = np.array([np.hstack((R[i], t[i].reshape((3, 1)))) for i in range(C)])
+        e = []
+        for i in range(M):
+            X = rc.triangulate(n[:, i, :2], P)
+            for c in range(C):
+                x2 = P[c] @ X.reshape((4, 1))
+                x2 = x2 / x2[2]
+                e.append(x2.flatten() - n[c, i, :].flatten())
+        e3d = []
+        for i in range(N):
+            e3 = 0
+            for c in range(1, C):
+                e3 += np.dot(vc[0, i] @ R[0], vc[c, i] @ R[c])
+            e3d.append(np.min([e3 / (C - 1), 1]))
+        e3d = np.arccos(e3d)
+        scores.append(np.linalg.norm(e) / M + np.linalg.norm(e3d) / N)
+        Rs.append(R); ts.append(t); sn.append(a); sm.append(b)
+
+    # the reference's full loop; capture the inputs of its final inlier fit to recover the masks
+    calls = []
+    orig = rc.calib_linear
+
+    def spy(v, nn):
+        calls.append((v.shape[1], nn.shape[1], v.copy(), nn.copy()))
+        return orig(v, nn)
+
+    rc.calib_linear = spy
+    try:
+        with quiet(), contextlib.redirect_stderr(io.StringIO()):
+            R_fin, t_fin, _ = rc.calib_linear_ransac(vc, n, sc.K, n_iter, th_2d, th_3d, seed)
+    finally:
+        rc.calib_linear = orig
+    v_in, n_in = calls[-1][2], calls[-1][3]
+    # inlier columns are an order-preserving subset: recover masks by exact column matching
+    mask_3d = np.zeros(N, bool); j = 0
+    for i in range(N):
+        if j < v_in.shape[1] and np.array_equal(vc[:, i], v_in[:, j]):
+            mask_3d[i] = True; j += 1
+    mask_2d = np.zeros(M, bool); j = 0
+    for i in range(M):
+        if j < n_in.shape[1] and np.array_equal(n[:, i], n_in[:, j]):
+            mask_2d[i] = True; j += 1
+    assert mask_3d.sum() == v_in.shape[1] and mask_2d.sum() == n_in.shape[1]
+    np.savez_compressed(os.path.join(OUT, f"ransac_{name}.npz"),
+                        p3d=sc.p3d, s3d=sc.s3d, p2d=sc.p2d, s2d=sc.s2d, K=sc.K, vc=vc, n=n,
+                        n_iter=n_iter, seed=seed, th_2d=th_2d, th_3d=th_3d,
+                        scores=np.array(scores), R_hyp=np.array(Rs), t_hyp=np.array(ts),
+                        sn=np.array(sn), sm=np.array(sm), best=int(np.argmin(scores)),
+                        mask_2d=mask_2d, mask_3d=mask_3d, R_fin=R_fin, t_fin=t_fin,
+                        versions=str(versions()))
+    print("wrote ransac", name, "N_o =", N, "M =", M, "best =", int(np.argmin(scores)),
+          "inliers", mask_2d.sum(), mask_3d.sum())
+
+
+if __name__ == "__main__":
+    os.makedirs(OUT, exist_ok=True)
+    gen_ba("small", dict(C=4, N=6, seed=11), list(range(17)), 1.0, 1.0, run_main=True)
+    gen_ba("partial", dict(C=5, N=8, seed=12, score_mode="uniform", p_drop_2d=0.3, p_drop_3d=0.1),
+           list(range(17)), 3.0, 7.0)
+    synadl_joints = list(range(23)) + [22, 23, 24]          # config.yaml:10-36 lists 22 twice
+    gen_ba("synadl26", dict(C=4, N=5, seed=13), synadl_joints, 1.0, 1.0)
+    gen_ba("gafa_lambda", dict(C=3, N=7, seed=14, score_mode="uniform"), list(range(17)), 1.0, 1e5)
+    gen_ransac("c4", dict(C=4, N=40, seed=21, p_drop_2d=0.1, p_drop_3d=0.05), 12, 0, 50.0, 5.0)
+    gen_ransac("c3", dict(C=3, N=30, seed=22, sigma_px=1.0), 8, 7, 50.0, 5.0)
