@@ -1,0 +1,85 @@
+"""ctypes binding of libbax.so (include/bax.h, include/rsx.h).  There is NO CPU fallback: if the
+library is missing or a call fails, an exception is raised."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libbax.so")
+
+_lib = None
+
+vp = C.c_void_p
+i32 = C.c_int
+i64 = C.c_int64
+f64 = C.c_double
+P_f64 = C.POINTER(C.c_double)
+P_i64 = C.POINTER(C.c_int64)
+P_i32 = C.POINTER(C.c_int32)
+
+_SIGS = {
+    "bax_last_error": (C.c_char_p, []),
+    "bax_version": (i32, []),
+    "bax_create": (i32, [i32, C.POINTER(vp)]),
+    "bax_destroy": (i32, [vp]),
+    "bax_problem_set": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, P_i32, f64, f64, vp]),
+    "bax_problem_dims": (i32, [vp, P_i64]),
+    "bax_residual": (i32, [vp, vp, vp, vp]),
+    "bax_residual_jacobian": (i32, [vp, vp, vp, vp, vp, vp, vp, vp]),
+    "bax_prior_jacobian": (i32, [vp, vp, vp, vp, vp]),
+    "bax_reduce_buffer": (i32, [vp, i32, C.POINTER(vp), P_i64]),
+    "bax_set_global_frames": (i32, [vp, i64]),
+    "bax_cost_begin": (i32, [vp, vp, vp]),
+    "bax_cost_mid": (i32, [vp, vp]),
+    "bax_cost_finish": (i32, [vp, P_f64, vp]),
+    "bax_linearize_begin": (i32, [vp, vp, vp]),
+    "bax_linearize_mid": (i32, [vp, vp]),
+    "bax_linearize_post": (i32, [vp, vp]),
+    "bax_linearize_finish": (i32, [vp, P_f64, vp]),
+    "bax_trial_begin": (i32, [vp, f64, vp]),
+    "bax_trial_mid": (i32, [vp, vp, i32, vp]),
+    "bax_trial_finish": (i32, [vp, P_f64, vp]),
+    "bax_triangulate": (i32, [vp, vp, vp, vp, P_i32, vp]),
+    "bax_timing_enable": (i32, [vp, i32]),
+    "bax_timing_read": (i32, [vp, P_f64, P_i64]),
+    "bax_timing_reset": (i32, [vp]),
+}
+
+BUF_BONE, BUF_COST, BUF_LIN, BUF_SCHUR, BUF_RHS2, BUF_STEP, BUF_NORM, BUF_GMAX = range(8)
+T_NAMES = ["rj", "build", "syrk", "dense", "backsub", "linearize", "cost", "other"]
+
+
+class BaxError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load libbax.so (once).  Raises if it has not been built — there is no fallback path."""
+    global _lib
+    if _lib is None:
+        if not os.path.isfile(LIB_PATH):
+            raise BaxError(f"{LIB_PATH} is missing: build it with __graft_entry__.build() "
+                           "(csrc/build.sh); this package has no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGS.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        try:
+            from . import _rsx_sigs
+            _rsx_sigs.declare(L)
+        except ImportError:
+            pass
+        _lib = L
+    return _lib
+
+
+def check(rc, what=""):
+    if rc != 0:
+        msg = lib().bax_last_error()
+        raise BaxError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")
+
+
+def exported_symbols():
+    return list(_SIGS.keys())

@@ -1,0 +1,496 @@
+"""Host side of the bundle-adjustment hot path: mirrors the reference's ba.py API
+(to_theta / from_theta / objfun / ba_main, reference ba.py:18-210) on top of libbax.so.
+
+PyTorch is used for device memory, streams and (multi-GPU) torch.distributed only; every
+numerical kernel is a hand-written sm_100a CUDA kernel behind include/bax.h.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import BaxError, check, lib
+
+# util.OP_BONE (reference util.py:129-145 via OP_KEY util.py:20-46)
+OP_BONE = np.array([[8, 1], [2, 5], [2, 3], [5, 6], [4, 3], [7, 6],
+                    [9, 8], [12, 8], [9, 10], [10, 11], [12, 13], [13, 14]], dtype=np.int64)
+EPS = float(np.finfo(np.float64).eps)
+
+
+# ----------------------------------------------------------------------------- SO(3) on the host
+def rodrigues(rvec):
+    """rvec -> R, the map cv2.Rodrigues applies at reference ba.py:29."""
+    r = np.asarray(rvec, dtype=np.float64).reshape(3)
+    th = math.sqrt(float(r @ r))
+    if th < EPS:
+        return np.eye(3)
+    k = r / th
+    c, s = math.cos(th), math.sin(th)
+    kx = np.array([[0, -k[2], k[1]], [k[2], 0, -k[0]], [-k[1], k[0], 0.0]])
+    return c * np.eye(3) + (1 - c) * np.outer(k, k) + s * kx
+
+
+def rodrigues_inv(R):
+    """R -> rvec as cv2.Rodrigues does at reference ba.py:19: SVD-project on SO(3) first (the linear
+    calibration returns non-orthonormal rotations), then the log map."""
+    U, _, Vt = np.linalg.svd(np.asarray(R, dtype=np.float64))
+    R = U @ Vt
+    r = np.array([R[2, 1] - R[1, 2], R[0, 2] - R[2, 0], R[1, 0] - R[0, 1]])
+    s = math.sqrt(float(r @ r) * 0.25)
+    c = min(1.0, max(-1.0, (np.trace(R) - 1) * 0.5))
+    th = math.acos(c)
+    if s < 1e-5:
+        if c > 0:
+            return np.zeros(3)
+        rx = math.sqrt(max((R[0, 0] + 1) * 0.5, 0.0))
+        ry = math.sqrt(max((R[1, 1] + 1) * 0.5, 0.0)) * (-1.0 if R[0, 1] < 0 else 1.0)
+        rz = math.sqrt(max((R[2, 2] + 1) * 0.5, 0.0)) * (-1.0 if R[0, 2] < 0 else 1.0)
+        if abs(rx) < abs(ry) and abs(rx) < abs(rz) and (R[1, 2] > 0) != (ry * rz > 0):
+            rz = -rz
+        v = np.array([rx, ry, rz])
+        return v * (th / np.linalg.norm(v))
+    return r * (0.5 * th / s)
+
+
+def to_theta(R, t, x):
+    """reference ba.py:18-20."""
+    rv = np.concatenate([rodrigues_inv(Rc) for Rc in R])
+    return np.concatenate([rv, np.asarray(t, dtype=np.float64).reshape(-1),
+                           np.asarray(x, dtype=np.float64).reshape(-1)])
+
+
+def from_theta(theta, C):
+    """reference ba.py:23-31."""
+    theta = np.asarray(theta, dtype=np.float64)
+    rv = theta[:3 * C].reshape(C, 3)
+    return (np.stack([rodrigues(r) for r in rv]), theta[3 * C:6 * C].reshape(C, 3, 1),
+            theta[6 * C:].reshape(-1, 3))
+
+
+# ----------------------------------------------------------------------------- device problem
+class _DevView:
+    """Zero-copy torch view of a device buffer owned by libbax (for torch.distributed.all_reduce)."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<f8", "data": (int(ptr), False),
+                                         "version": 2}
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class BAProblem:
+    """One BA problem bound to one GPU.  Arguments are what reference ba.objfun receives
+    (ba.py:113): K (C,3,3), sp2d (C,N*J,2) or (C,N,J,2), ss2d (C,N,J), sp3d (C,N,J3,3), ss3d (C,N,J3).
+
+    Multi-GPU: give every rank its own contiguous block of frames and a torch.distributed
+    `group`; the small packed buffers are all-reduced between the kernel phases (include/bax.h)."""
+
+    def __init__(self, K, sp2d, ss2d, sp3d, ss3d, bone_idx=OP_BONE, lambda1=1.0, lambda2=1.0,
+                 device=None, group=None, n_frames_global=None):
+        if not torch.cuda.is_available():
+            raise BaxError("no CUDA device: this package has no CPU fallback")
+        self.L = lib()
+        self.dev = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        ss2d_t = torch.as_tensor(ss2d)
+        C_, N_, J_ = ss2d_t.shape
+        self.C, self.N, self.J = int(C_), int(N_), int(J_)
+        self.P = self.N * self.J
+        f = dict(dtype=torch.float64, device=self.dev)
+        with torch.cuda.device(self.dev):
+            self.K = torch.as_tensor(K).to(**f).contiguous()
+            self.y = torch.as_tensor(sp2d).to(**f).contiguous().reshape(self.C, self.P, 2)
+            self.s = ss2d_t.to(**f).contiguous().reshape(self.C, self.P)
+            p3 = torch.as_tensor(sp3d).to(**f).contiguous() if sp3d is not None else None
+            s3 = torch.as_tensor(ss3d).to(**f).contiguous() if ss3d is not None else None
+            self.J3 = int(p3.shape[2]) if p3 is not None else self.J
+            bones = np.ascontiguousarray(np.asarray(bone_idx), dtype=np.int32)
+            self.B = int(bones.shape[0])
+            self.bones = bones
+            self.lambda1, self.lambda2 = float(lambda1), float(lambda2)
+            h = C.c_void_p()
+            check(self.L.bax_create(self.dev.index or 0, C.byref(h)), "bax_create")
+            self.h = h
+            check(self.L.bax_problem_set(self.h, self.C, self.N, self.J, self.J3, self.B,
+                                         self.K.data_ptr(), self.y.data_ptr(), self.s.data_ptr(),
+                                         p3.data_ptr() if p3 is not None else None,
+                                         s3.data_ptr() if s3 is not None else None,
+                                         bones.ctypes.data_as(_lib.P_i32), self.lambda1, self.lambda2, _stream()),
+                  "bax_problem_set")
+            d = (C.c_int64 * 6)()
+            check(self.L.bax_problem_dims(self.h, d), "bax_problem_dims")
+            self.n_vis, self.n_v3d, self.m, self.n, self.aug_rows, _ = [int(v) for v in d]
+            self.step = torch.zeros(self.n, **f)
+        self.group = group
+        self._views = {}
+        if n_frames_global is not None:
+            check(self.L.bax_set_global_frames(self.h, int(n_frames_global)), "bax_set_global_frames")
+        self._out4 = (C.c_double * 4)()
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.bax_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- helpers
+    def _dev_theta(self, theta):
+        if isinstance(theta, torch.Tensor) and theta.device == self.dev and theta.dtype == torch.float64:
+            return theta.contiguous()
+        return torch.as_tensor(np.asarray(theta, dtype=np.float64)).to(self.dev)
+
+    def _allreduce(self, which, op=None):
+        if self.group is None:
+            return
+        import torch.distributed as dist
+        if which not in self._views:
+            p, n = C.c_void_p(), C.c_int64()
+            check(self.L.bax_reduce_buffer(self.h, which, C.byref(p), C.byref(n)), "bax_reduce_buffer")
+            self._views[which] = torch.as_tensor(_DevView(p.value, n.value), device=self.dev)
+        dist.all_reduce(self._views[which], op=op or dist.ReduceOp.SUM, group=self.group)
+
+    # ---- reference-shaped evaluations
+    def residual(self, theta):
+        """ba.objfun(theta, ...) -> (m,) torch tensor on the device."""
+        th = self._dev_theta(theta)
+        out = torch.empty(self.m, dtype=torch.float64, device=self.dev)
+        with torch.cuda.device(self.dev):
+            check(self.L.bax_residual(self.h, th.data_ptr(), out.data_ptr(), _stream()), "bax_residual")
+        self._keep = th
+        return out
+
+    def residual_jacobian(self, theta, with_index=True, out=None):
+        """Fused residual + Jacobian blocks of the visible reprojection rows (device tensors):
+        r2 (n_vis,2), Jcam (n_vis,2,6), Jpt (n_vis,2,3), obs_cam, obs_pt (n_vis,) int32."""
+        th = self._dev_theta(theta)
+        f = dict(dtype=torch.float64, device=self.dev)
+        if out is None:
+            r2 = torch.empty(self.n_vis, 2, **f)
+            Jc = torch.empty(self.n_vis, 2, 6, **f)
+            Jp = torch.empty(self.n_vis, 2, 3, **f)
+            oc = torch.empty(self.n_vis, dtype=torch.int32, device=self.dev) if with_index else None
+            op = torch.empty(self.n_vis, dtype=torch.int32, device=self.dev) if with_index else None
+        else:
+            r2, Jc, Jp, oc, op = out
+        with torch.cuda.device(self.dev):
+            check(self.L.bax_residual_jacobian(self.h, th.data_ptr(), r2.data_ptr(), Jc.data_ptr(), Jp.data_ptr(),
+                                               oc.data_ptr() if oc is not None else None,
+                                               op.data_ptr() if op is not None else None, _stream()),
+                  "bax_residual_jacobian")
+        self._keep = th
+        return r2, Jc, Jp, oc, op
+
+    def jacobian(self, theta):
+        """Analytic Jacobian of ba.objfun as scipy CSR (m x n), assembled on the host from the device
+        blocks.  (The reference has none: SciPy finite-differences ba.objfun, ba.py:187-206.)"""
+        import scipy.sparse as sp
+        th = self._dev_theta(theta)
+        r2, Jc, Jp, oc, op = self.residual_jacobian(th)
+        Cn, nv = self.C, self.n_vis
+        oc = oc.cpu().numpy().astype(np.int64); op = op.cpu().numpy().astype(np.int64)
+        Jc = Jc.cpu().numpy(); Jp = Jp.cpu().numpy()
+        rows = (2 * np.arange(nv)[:, None] + np.arange(2)[None, :])              # (nv,2)
+        cols_r = 3 * oc[:, None] + np.arange(3)[None, :]
+        cols_t = 3 * Cn + 3 * oc[:, None] + np.arange(3)[None, :]
+        cols_p = 6 * Cn + 3 * op[:, None] + np.arange(3)[None, :]
+        R_, C_, V_ = [], [], []
+        for cols, blk in ((cols_r, Jc[:, :, :3]), (cols_t, Jc[:, :, 3:]), (cols_p, Jp)):
+            R_.append(np.broadcast_to(rows[:, :, None], (nv, 2, 3)).reshape(-1))
+            C_.append(np.broadcast_to(cols[:, None, :], (nv, 2, 3)).reshape(-1))
+            V_.append(blk.reshape(-1))
+        f = dict(dtype=torch.float64, device=self.dev)
+        Jv = torch.zeros(max(self.n_v3d, 1), 3 * Cn, **f)
+        Jb = torch.zeros(self.N, max(self.B, 1), 3, **f)
+        with torch.cuda.device(self.dev):
+            check(self.L.bax_prior_jacobian(self.h, th.data_ptr(), Jv.data_ptr(), Jb.data_ptr(), _stream()),
+                  "bax_prior_jacobian")
+        if self.n_v3d:
+            Jv = Jv.cpu().numpy()
+            R_.append(np.repeat(2 * nv + np.arange(self.n_v3d), 3 * Cn))
+            C_.append(np.tile(np.arange(3 * Cn), self.n_v3d))
+            V_.append(Jv.reshape(-1))
+        if self.B:
+            Jb = Jb.cpu().numpy()
+            row0 = 2 * nv + self.n_v3d
+            n_idx = np.arange(self.N)
+            for b in range(self.B):
+                for e, sg in ((0, 1.0), (1, -1.0)):
+                    pcol = 6 * Cn + 3 * (n_idx * self.J + int(self.bones[b, e]))
+                    R_.append(np.full(3 * self.N, row0 + b))
+                    C_.append((pcol[:, None] + np.arange(3)[None, :]).reshape(-1))
+                    V_.append((sg * Jb[:, b, :]).reshape(-1))
+        return sp.csr_matrix((np.concatenate(V_), (np.concatenate(R_), np.concatenate(C_))),
+                             shape=(self.m, self.n))
+
+    # ---- LM building blocks (phases split where a frame-sharded run all-reduces)
+    def cost(self, theta):
+        th = self._dev_theta(theta)
+        self._keep_cost = th
+        st = _stream()
+        with torch.cuda.device(self.dev):
+            check(self.L.bax_cost_begin(self.h, th.data_ptr(), st), "bax_cost_begin")
+            self._allreduce(_lib.BUF_BONE)
+            check(self.L.bax_cost_mid(self.h, st), "bax_cost_mid")
+            self._allreduce(_lib.BUF_COST)
+            out = C.c_double()
+            check(self.L.bax_cost_finish(self.h, C.byref(out), st), "bax_cost_finish")
+        return out.value
+
+    def linearize(self, theta):
+        """-> (cost, ||g||_inf, ||g||_2, ||theta||_2); keeps V_p, g_p, H_cc on the device."""
+        th = self._dev_theta(theta)
+        self._keep_lin = th
+        st = _stream()
+        with torch.cuda.device(self.dev):
+            check(self.L.bax_linearize_begin(self.h, th.data_ptr(), st), "bax_linearize_begin")
+            self._allreduce(_lib.BUF_BONE)
+            check(self.L.bax_linearize_mid(self.h, st), "bax_linearize_mid")
+            self._allreduce(_lib.BUF_LIN)
+            check(self.L.bax_linearize_post(self.h, st), "bax_linearize_post")
+            if self.group is not None:
+                import torch.distributed as dist
+                self._allreduce(_lib.BUF_NORM)
+                self._allreduce(_lib.BUF_GMAX, dist.ReduceOp.MAX)
+            check(self.L.bax_linearize_finish(self.h, self._out4, st), "bax_linearize_finish")
+        return tuple(self._out4)
+
+    def trial(self, alpha, need_phi_prime=True):
+        """Solve (J^T J + alpha I) p = -g; p lands in self.step (device).
+        -> (||p||^2, g.p, p^T (J^T J + alpha I)^-1 p)."""
+        st = _stream()
+        with torch.cuda.device(self.dev):
+            check(self.L.bax_trial_begin(self.h, float(alpha), st), "bax_trial_begin")
+            self._allreduce(_lib.BUF_SCHUR)
+            check(self.L.bax_trial_mid(self.h, self.step.data_ptr(), 1 if need_phi_prime else 0, st), "bax_trial_mid")
+            self._allreduce(_lib.BUF_RHS2)
+            check(self.L.bax_trial_finish(self.h, self._out4, st), "bax_trial_finish")
+        pn2, gp, ptq = self._out4[0], self._out4[1], self._out4[2]
+        if not (math.isfinite(pn2) and math.isfinite(gp)):
+            raise BaxError(f"non-finite trial step at alpha={alpha}: reduced camera system not SPD")
+        return pn2, gp, ptq
+
+    def triangulate(self, R_w2c, t_w2c):
+        """util.triangulate_with_conf (reference util.py:325-354) -> (N,J,3) numpy."""
+        f = dict(dtype=torch.float64, device=self.dev)
+        R = torch.as_tensor(np.asarray(R_w2c, dtype=np.float64)).to(**f).contiguous()
+        t = torch.as_tensor(np.asarray(t_w2c, dtype=np.float64).reshape(self.C, 3)).to(**f).contiguous()
+        X = torch.empty(self.P, 3, **f)
+        st = C.c_int32(0)
+        with torch.cuda.device(self.dev):
+            check(self.L.bax_triangulate(self.h, R.data_ptr(), t.data_ptr(), X.data_ptr(), C.byref(st), _stream()),
+                  "bax_triangulate")
+        if st.value == 1:
+            raise Exception("not enough constraint")          # reference util.py:320-321
+        return X.cpu().numpy().reshape(self.N, self.J, 3)
+
+    # ---- timing hooks
+    def timing(self, on=True):
+        check(self.L.bax_timing_enable(self.h, 1 if on else 0))
+        check(self.L.bax_timing_reset(self.h))
+
+    def timing_read(self):
+        ms = (C.c_double * 8)(); nl = (C.c_int64 * 8)()
+        check(self.L.bax_timing_read(self.h, ms, nl))
+        return {k: (ms[i], int(nl[i])) for i, k in enumerate(_lib.T_NAMES)}
+
+
+# ----------------------------------------------------------------------------- trust-region driver
+def _solve_tr(prob, Delta, g_norm2, initial_alpha, rtol=0.01, max_iter=10):
+    """More'-Sorensen root-finding of ||p(alpha)|| = Delta (scipy/optimize/_lsq/common.py:57-168), with
+    every phi / phi' evaluation a damped Schur solve on the GPU instead of an SVD of the dense Jacobian.
+    The exact Jacobian has a 6-dimensional gauge null space, so SciPy's `full_rank` branch (an undamped
+    Gauss-Newton step) never applies and alpha_lower starts at 0."""
+    alpha_upper = g_norm2 / Delta
+    alpha_lower = 0.0
+    if initial_alpha is None or initial_alpha == 0:
+        alpha = max(0.001 * alpha_upper, (alpha_lower * alpha_upper) ** 0.5)
+    else:
+        alpha = initial_alpha
+    it = 0
+    for it in range(max_iter):
+        if alpha < alpha_lower or alpha > alpha_upper or not alpha > 0:
+            alpha = max(0.001 * alpha_upper, (alpha_lower * alpha_upper) ** 0.5)
+        pn2, gp, ptq = prob.trial(alpha, True)
+        p_norm = math.sqrt(pn2)
+        phi = p_norm - Delta
+        phi_prime = -ptq / p_norm
+        if phi < 0:
+            alpha_upper = alpha
+        ratio = phi / phi_prime
+        alpha_lower = max(alpha_lower, alpha - ratio)
+        alpha -= (phi + Delta) * ratio / Delta
+        if abs(phi) < rtol * Delta:
+            break
+    if not alpha > 0:
+        alpha = max(0.001 * alpha_upper, (alpha_lower * alpha_upper) ** 0.5)
+    pn2, gp, _ = prob.trial(alpha, False)
+    return alpha, it + 1, math.sqrt(pn2), gp
+
+
+def _update_tr_radius(Delta, actual, predicted, step_norm, bound_hit):
+    """scipy/optimize/_lsq/common.py:222-248."""
+    if predicted > 0:
+        ratio = actual / predicted
+    elif predicted == actual == 0:
+        ratio = 1
+    else:
+        ratio = 0
+    if ratio < 0.25:
+        Delta = 0.25 * step_norm
+    elif ratio > 0.75 and bound_hit:
+        Delta *= 2.0
+    return Delta, ratio
+
+
+def _check_termination(dF, F, dx_norm, x_norm, ratio, ftol, xtol):
+    """scipy/optimize/_lsq/common.py:705-717."""
+    ftol_ok = dF < ftol * F and ratio > 0.25
+    xtol_ok = dx_norm < xtol * (xtol + x_norm)
+    if ftol_ok and xtol_ok:
+        return 4
+    if ftol_ok:
+        return 2
+    if xtol_ok:
+        return 3
+    return None
+
+
+TERMINATION_MESSAGES = {0: "The maximum number of function evaluations is exceeded.",
+                        1: "`gtol` termination condition is satisfied.",
+                        2: "`ftol` termination condition is satisfied.",
+                        3: "`xtol` termination condition is satisfied.",
+                        4: "Both `ftol` and `xtol` termination conditions are satisfied."}
+
+
+def trf_schur(prob, theta0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, verbose=0, callback=None):
+    """Trust-region-reflective loop of SciPy's `trf_no_bounds` (scipy/optimize/_lsq/trf.py:415-587,
+    x_scale = 1, tr_solver = 'exact') — the solver reference ba.py:187-206 runs — with the Jacobian,
+    normal equations and damped solves on the GPU.  Returns a dict like OptimizeResult."""
+    x = prob._dev_theta(theta0).clone()
+    cost, g_inf, g_2, x_norm = prob.linearize(x)
+    if not math.isfinite(cost):
+        raise ValueError("Residuals are not finite in the initial point.")
+    initial_cost = cost
+    nfev, njev = 1, 1
+    n = prob.n
+    if max_nfev is None:
+        max_nfev = 100 * n
+    Delta = x_norm if x_norm > 0 else 1.0
+    alpha = 0.0
+    status = None
+    iteration = 0
+    history = []
+    x_new = torch.empty_like(x)
+    while True:
+        if g_inf < gtol:
+            status = 1
+        if status is not None or nfev == max_nfev:
+            break
+        actual_reduction = -1.0
+        cost_new = cost
+        while actual_reduction <= 0 and nfev < max_nfev:
+            alpha, n_it, p_norm, gdotp = _solve_tr(prob, Delta, g_2, alpha)
+            kappa = Delta / p_norm                   # SciPy rescales the step onto the boundary
+            # -(0.5 ||J s||^2 + g.s) with s = kappa p and p^T J^T J p = -g.p - alpha ||p||^2
+            predicted = -(0.5 * kappa * kappa * (-gdotp - alpha * p_norm * p_norm) + kappa * gdotp)
+            torch.add(x, prob.step, alpha=kappa, out=x_new)
+            cost_new = prob.cost(x_new)
+            nfev += 1
+            step_norm = Delta
+            if not math.isfinite(cost_new):
+                Delta = 0.25 * step_norm
+                continue
+            actual_reduction = cost - cost_new
+            Delta_new, ratio = _update_tr_radius(Delta, actual_reduction, predicted, step_norm,
+                                                 step_norm > 0.95 * Delta)
+            history.append(dict(alpha=alpha, Delta=Delta, step_norm=step_norm, cost_new=cost_new,
+                                pred=predicted, act=actual_reduction, n_it=n_it))
+            status = _check_termination(actual_reduction, cost, step_norm, x_norm, ratio, ftol, xtol)
+            if status is not None:
+                break
+            alpha *= Delta / Delta_new
+            Delta = Delta_new
+        if actual_reduction > 0:
+            x, x_new = x_new, x
+            cost, g_inf, g_2, x_norm = prob.linearize(x)
+            njev += 1
+        iteration += 1
+        if callback is not None:
+            callback(iteration, cost, nfev)
+    if status is None:
+        status = 0
+    if verbose:
+        print(TERMINATION_MESSAGES[status])
+        print(f"Function evaluations {nfev}, initial cost {initial_cost:.4e}, final cost {cost:.4e}, "
+              f"first-order optimality {g_inf:.2e}.")
+    return dict(x=x, cost=cost, optimality=g_inf, nfev=nfev, njev=njev, status=status,
+                iterations=iteration, history=history, message=TERMINATION_MESSAGES[status])
+
+
+# ----------------------------------------------------------------------------- reference entry points
+_cache = {}
+
+
+def _problem_for(K, sp2d, ss2d, sp3d, ss3d, bone_idx, C, N, J, lambda1, lambda2):
+    key = (id(K), id(sp2d), id(ss2d), id(sp3d), id(ss3d), C, N, J, float(lambda1), float(lambda2))
+    hit = _cache.get("p")
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    if hit is not None:
+        hit[1].close()
+    prob = BAProblem(K, np.asarray(sp2d).reshape(C, N * J, 2), np.asarray(ss2d).reshape(C, N, J), sp3d, ss3d,
+                     bone_idx, lambda1, lambda2)
+    _cache["p"] = (key, prob, (K, sp2d, ss2d, sp3d, ss3d))     # keep the arrays alive: the key uses id()
+    return prob
+
+
+def objfun(params, K, sp2d, ss2d, sp3d, ss3d, bone_idx, C, N, J, lambda1, lambda2):
+    """Drop-in for reference ba.objfun (ba.py:113-140): NumPy in, NumPy (m,) out, computed on the GPU."""
+    prob = _problem_for(K, sp2d, ss2d, sp3d, ss3d, bone_idx, C, N, J, lambda1, lambda2)
+    return prob.residual(params).cpu().numpy()
+
+
+def jacobian(params, K, sp2d, ss2d, sp3d, ss3d, bone_idx, C, N, J, lambda1, lambda2):
+    """Analytic Jacobian matching `objfun` (scipy CSR); usable as least_squares(jac=...)."""
+    prob = _problem_for(K, sp2d, ss2d, sp3d, ss3d, bone_idx, C, N, J, lambda1, lambda2)
+    return prob.jacobian(params)
+
+
+def ba_main(camid, K, R_w2c, t_w2c, sp2d, ss2d, sp3d, ss3d, lambda1, lambda2, *,
+            ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, verbose=True, return_info=False):
+    """Drop-in for reference ba.ba_main (ba.py:157-210): triangulate the start, print the three initial
+    mean costs, minimise ba.objfun by trust-region least squares (ftol=1e-4), unpack."""
+    C = len(camid)
+    N, J = sp2d.shape[1], sp2d.shape[2]
+    prob = BAProblem(K, np.asarray(sp2d).reshape(C, N * J, 2), ss2d, sp3d, ss3d, OP_BONE, lambda1, lambda2)
+    try:
+        x_all = prob.triangulate(R_w2c, t_w2c).reshape(N * J, 3)
+        theta0 = to_theta(R_w2c, t_w2c, x_all)
+        if not np.all(np.isfinite(theta0)):
+            # NaN from an unseen / single-view point reaches SciPy's bounds check in the reference
+            raise ValueError("Initial guess is outside of provided bounds")
+        if verbose:
+            f0 = prob.residual(theta0).cpu().numpy()
+            e1 = f0[:2 * prob.n_vis]
+            e2 = f0[2 * prob.n_vis:2 * prob.n_vis + prob.n_v3d] / (lambda1 if lambda1 != 0 else 1.0)
+            e3 = f0[2 * prob.n_vis + prob.n_v3d:] / (lambda2 if lambda2 != 0 else 1.0)
+            print(f"Initial mean NLL: {np.mean(e1 * e1)}")
+            print(f"Initial mean 3D variance: {np.mean(e2 * e2)}")
+            print(f"Initial mean bone-length variance: {np.mean(e3 * e3)}")
+        res = trf_schur(prob, theta0, ftol=ftol, xtol=xtol, gtol=gtol, max_nfev=max_nfev, verbose=1 if verbose else 0)
+        theta = res["x"].cpu().numpy()
+        res["x"] = theta
+    finally:
+        prob.close()
+    R, t, x = from_theta(theta, C)
+    return (R, t, x, res) if return_info else (R, t, x)

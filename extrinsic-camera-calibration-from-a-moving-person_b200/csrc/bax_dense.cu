@@ -1,0 +1,328 @@
+// Reduced camera system: FP64 single-CTA blocked Cholesky + triangular solves (SPD because alpha > 0).
+#include "bax_internal.cuh"
+
+#define DN_THREADS 1024
+#define NBK 32
+#define LDS_ 33
+
+// In-place lower Cholesky of A (n x n, row-major, leading dimension ld, global/L2 resident).
+// Dg: [32][33] shared, Pn: [(n-32)][33] shared.  Right-looking, 32-wide panels, 4x4 register tiles.
+__device__ void chol_blocked(double* __restrict__ A, int n, int ld, double* Dg, double* Pn) {
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
+  for (int j0 = 0; j0 < n; j0 += NBK) {
+    const int nb = min(NBK, n - j0);
+    for (int idx = tid; idx < nb * nb; idx += nt) {
+      int r = idx / nb, c = idx % nb;
+      Dg[r * LDS_ + c] = A[(size_t)(j0 + r) * ld + j0 + c];
+    }
+    __syncthreads();
+    if (warp == 0) {
+      for (int k = 0; k < nb; ++k) {
+        double dkk = sqrt(Dg[k * LDS_ + k]);
+        __syncwarp();
+        if (lane == k) Dg[k * LDS_ + k] = dkk;
+        if (lane > k && lane < nb) Dg[lane * LDS_ + k] /= dkk;
+        __syncwarp();
+        if (lane > k && lane < nb) {
+          double lk = Dg[lane * LDS_ + k];
+          for (int c = k + 1; c <= lane; ++c) Dg[lane * LDS_ + c] -= lk * Dg[c * LDS_ + k];
+        }
+        __syncwarp();
+      }
+    }
+    __syncthreads();
+    for (int idx = tid; idx < nb * nb; idx += nt) {
+      int r = idx / nb, c = idx % nb;
+      if (c <= r) A[(size_t)(j0 + r) * ld + j0 + c] = Dg[r * LDS_ + c];
+    }
+    const int base = j0 + nb, m = n - base;
+    if (m > 0) {
+      for (int idx = tid; idx < m * nb; idx += nt) {
+        int r = idx / nb, c = idx % nb;
+        Pn[r * LDS_ + c] = A[(size_t)(base + r) * ld + j0 + c];
+      }
+      __syncthreads();
+      for (int r = tid; r < m; r += nt) {        // L21 = A21 L11^-T, one row per thread
+        double* row = Pn + r * LDS_;
+        for (int t = 0; t < nb; ++t) {
+          double v = row[t];
+          for (int u = 0; u < t; ++u) v -= row[u] * Dg[t * LDS_ + u];
+          row[t] = v / Dg[t * LDS_ + t];
+        }
+      }
+      __syncthreads();
+      for (int idx = tid; idx < m * nb; idx += nt) {
+        int r = idx / nb, c = idx % nb;
+        A[(size_t)(base + r) * ld + j0 + c] = Pn[r * LDS_ + c];
+      }
+      const int m4 = (m + 3) >> 2;
+      for (int tile = tid; tile < m4 * m4; tile += nt) {
+        int ti = tile / m4, tk = tile % m4;
+        if (tk > ti) continue;
+        double acc[4][4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+        int ra[4], rk[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) { ra[a] = min(4 * ti + a, m - 1); rk[a] = min(4 * tk + a, m - 1); }
+        for (int t = 0; t < nb; ++t) {
+          double pa[4], pk[4];
+#pragma unroll
+          for (int a = 0; a < 4; ++a) { pa[a] = Pn[ra[a] * LDS_ + t]; pk[a] = Pn[rk[a] * LDS_ + t]; }
+#pragma unroll
+          for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] += pa[a] * pk[b];
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) {
+            int i = 4 * ti + a, k = 4 * tk + b;
+            if (i < m && k <= i) A[(size_t)(base + i) * ld + base + k] -= acc[a][b];
+          }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// x <- L^-1 x (fwd) or L^-T x (bwd); x in shared memory, L lower in global.
+__device__ void trsv_blocked(const double* __restrict__ A, int n, int ld, double* x, double* Dg, bool transpose) {
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
+  const int nblk = (n + NBK - 1) / NBK;
+  for (int bi = 0; bi < nblk; ++bi) {
+    const int j0 = transpose ? (nblk - 1 - bi) * NBK : bi * NBK;
+    const int nb = min(NBK, n - j0);
+    for (int idx = tid; idx < nb * nb; idx += nt) {
+      int r = idx / nb, c = idx % nb;
+      Dg[r * LDS_ + c] = A[(size_t)(j0 + r) * ld + j0 + c];
+    }
+    __syncthreads();
+    if (warp == 0) {
+      if (!transpose) {
+        for (int k = 0; k < nb; ++k) {
+          double xk = x[j0 + k] / Dg[k * LDS_ + k];
+          __syncwarp();
+          if (lane == k) x[j0 + k] = xk;
+          if (lane > k && lane < nb) x[j0 + lane] -= Dg[lane * LDS_ + k] * xk;
+          __syncwarp();
+        }
+      } else {
+        for (int k = nb - 1; k >= 0; --k) {
+          double xk = x[j0 + k] / Dg[k * LDS_ + k];
+          __syncwarp();
+          if (lane == k) x[j0 + k] = xk;
+          if (lane < k) x[j0 + lane] -= Dg[k * LDS_ + lane] * xk;
+          __syncwarp();
+        }
+      }
+    }
+    __syncthreads();
+    if (!transpose) {
+      for (int i = j0 + nb + tid; i < n; i += nt) {
+        double v = x[i];
+        const double* row = A + (size_t)i * ld + j0;
+        for (int t = 0; t < nb; ++t) v -= row[t] * x[j0 + t];
+        x[i] = v;
+      }
+    } else {
+      for (int i = tid; i < j0; i += nt) {
+        double v = x[i];
+        for (int t = 0; t < nb; ++t) v -= A[(size_t)(j0 + t) * ld + i] * x[j0 + t];
+        x[i] = v;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// workspace layout (doubles): Sf [n*n] | Z [B*n] | pc [n] | qc [n] | LT [B*B] | hz [B] | w [B]
+struct DenseWs { double *Sf, *Z, *pc, *qc, *LT, *hz, *w; };
+__device__ __host__ inline DenseWs dense_ws(double* ws, int n, int B) {
+  DenseWs d; d.Sf = ws; d.Z = d.Sf + (size_t)n * n; d.pc = d.Z + (size_t)BAX_MAX_B * n; d.qc = d.pc + n;
+  d.LT = d.qc + n; d.hz = d.LT + BAX_MAX_B * BAX_MAX_B; d.w = d.hz + BAX_MAX_B; return d;
+}
+
+// small serial helpers on B x B (B <= 16) systems held in shared memory
+__device__ void small_chol(double* T, int B) {     // in place lower, row-major ld = BAX_MAX_B
+  for (int k = 0; k < B; ++k) {
+    double d = sqrt(T[k * BAX_MAX_B + k]); T[k * BAX_MAX_B + k] = d;
+    for (int i = k + 1; i < B; ++i) T[i * BAX_MAX_B + k] /= d;
+    for (int i = k + 1; i < B; ++i)
+      for (int j = k + 1; j <= i; ++j) T[i * BAX_MAX_B + j] -= T[i * BAX_MAX_B + k] * T[j * BAX_MAX_B + k];
+  }
+}
+__device__ void small_fwd(const double* L, int B, double* v) {
+  for (int a = 0; a < B; ++a) { double s = v[a]; for (int b = 0; b < a; ++b) s -= L[a * BAX_MAX_B + b] * v[b]; v[a] = s / L[a * BAX_MAX_B + a]; }
+}
+__device__ void small_bwd(const double* L, int B, double* v) {
+  for (int a = B - 1; a >= 0; --a) { double s = v[a]; for (int b = a + 1; b < B; ++b) s -= L[b * BAX_MAX_B + a] * v[b]; v[a] = s / L[a * BAX_MAX_B + a]; }
+}
+
+__global__ void __launch_bounds__(DN_THREADS)
+k_dense_solve1(const double* __restrict__ schur, int R, const double* __restrict__ lin, int n, int B, double alpha,
+               double* __restrict__ ws, double* __restrict__ coef) {
+  extern __shared__ double smem[];
+  double* Dg = smem;                        // 32*33
+  double* xs = Dg + NBK * LDS_;             // n
+  double* sLT = xs + ((n + 1) & ~1);        // 16*16
+  double* sh = sLT + BAX_MAX_B * BAX_MAX_B; // 16 (h0 / hz)
+  double* Pn = sh + BAX_MAX_B;              // (n-32)*33
+  const int tid = threadIdx.x, nt = blockDim.x;
+  DenseWs d = dense_ws(ws, n, B);
+  const double* Hcc = lin; const double* gc = lin + (size_t)n * n;
+  // 1. T = I + Ut^T Ut, Cholesky; hz = LT^-1 h0
+  for (int i = tid; i < BAX_MAX_B * BAX_MAX_B; i += nt) {
+    int a = i / BAX_MAX_B, b = i % BAX_MAX_B;
+    sLT[i] = (a < B && b < B) ? schur[(size_t)(n + a) * R + n + b] + (a == b ? 1.0 : 0.0) : (a == b ? 1.0 : 0.0);
+  }
+  if (tid < BAX_MAX_B) sh[tid] = tid < B ? schur[(size_t)(n + tid) * R + n + B] : 0.0;
+  __syncthreads();
+  if (tid == 0) { small_chol(sLT, B); small_fwd(sLT, B, sh); }
+  __syncthreads();
+  for (int i = tid; i < BAX_MAX_B * BAX_MAX_B; i += nt) d.LT[i] = sLT[i];
+  if (tid < BAX_MAX_B) d.hz[tid] = sh[tid];
+  // 2. Z = LT^-1 G^T  (B x n), one camera parameter per thread
+  for (int i = tid; i < n; i += nt) {
+    double z[BAX_MAX_B];
+#pragma unroll
+    for (int a = 0; a < BAX_MAX_B; ++a) z[a] = a < B ? schur[(size_t)i * R + n + a] : 0.0;
+#pragma unroll
+    for (int a = 0; a < BAX_MAX_B; ++a) {
+      double s = z[a];
+#pragma unroll
+      for (int b = 0; b < BAX_MAX_B; ++b) if (b < a) s -= sLT[a * BAX_MAX_B + b] * z[b];
+      z[a] = s / sLT[a * BAX_MAX_B + a];
+    }
+#pragma unroll
+    for (int a = 0; a < BAX_MAX_B; ++a) if (a < B) d.Z[(size_t)a * n + i] = z[a];
+    double r = -gc[i] - schur[(size_t)i * R + n + B];
+#pragma unroll
+    for (int a = 0; a < BAX_MAX_B; ++a) if (a < B) r += z[a] * sh[a];
+    xs[i] = r;
+  }
+  __syncthreads();
+  // 3. S = Hcc + alpha I - Y Y^T + Z^T Z   (lower triangle)
+  for (int idx = tid; idx < n * n; idx += nt) {
+    int i = idx / n, j = idx % n;
+    if (j > i) continue;
+    double v = Hcc[idx] - schur[(size_t)i * R + j] + (i == j ? alpha : 0.0);
+    for (int a = 0; a < B; ++a) v += d.Z[(size_t)a * n + i] * d.Z[(size_t)a * n + j];
+    d.Sf[idx] = v;
+  }
+  __syncthreads();
+  // 4. factor and solve
+  chol_blocked(d.Sf, n, n, Dg, Pn);
+  trsv_blocked(d.Sf, n, n, xs, Dg, false);
+  trsv_blocked(d.Sf, n, n, xs, Dg, true);
+  for (int i = tid; i < n; i += nt) { d.pc[i] = xs[i]; coef[i] = xs[i]; }
+  // 5. w = T^-1 (h0 - G^T pc)
+  if (tid < B) {
+    double hv = schur[(size_t)(n + tid) * R + n + B];
+    for (int i = 0; i < n; ++i) hv -= schur[(size_t)i * R + n + tid] * xs[i];
+    sh[tid] = hv;
+  }
+  __syncthreads();
+  if (tid == 0) { small_fwd(sLT, B, sh); small_bwd(sLT, B, sh); }
+  __syncthreads();
+  if (tid < B) { d.w[tid] = sh[tid]; coef[n + tid] = sh[tid]; }
+}
+
+// second reduced solve for phi'(alpha) and the step scalars
+//   rhs2 = [ rhs0' (n) | h0' (B) | sum|p_p|^2 | sum g_p.p_p | sum |L^-1 p_p|^2 | . ]
+//   out  = { |p|^2, g.p, p^T (H + alpha I)^-1 p, 0 }
+__global__ void __launch_bounds__(DN_THREADS)
+k_dense_solve2(const double* __restrict__ schur, int R, const double* __restrict__ lin, int n, int B,
+               const double* __restrict__ rhs2, double* __restrict__ ws, int need_phi, double* __restrict__ out) {
+  extern __shared__ double smem[];
+  double* Dg = smem;
+  double* xs = Dg + NBK * LDS_;
+  double* sLT = xs + ((n + 1) & ~1);
+  double* sh = sLT + BAX_MAX_B * BAX_MAX_B;
+  double* sred = sh + BAX_MAX_B;            // 4*32
+  const int tid = threadIdx.x, nt = blockDim.x;
+  DenseWs d = dense_ws(ws, n, B);
+  const double* gc = lin + (size_t)n * n;
+  double acc[4] = {0, 0, 0, 0};             // |pc|^2, gc.pc, pc.qc, rhs0'.qc
+  if (need_phi) {
+    for (int i = tid; i < BAX_MAX_B * BAX_MAX_B; i += nt) sLT[i] = d.LT[i];
+    if (tid < BAX_MAX_B) sh[tid] = tid < B ? rhs2[n + tid] : 0.0;
+    __syncthreads();
+    if (tid == 0) small_fwd(sLT, B, sh);    // hz' = LT^-1 h0'
+    __syncthreads();
+    for (int i = tid; i < n; i += nt) {
+      double r = d.pc[i] - rhs2[i];
+      for (int a = 0; a < B; ++a) r += d.Z[(size_t)a * n + i] * sh[a];
+      xs[i] = r;
+    }
+    __syncthreads();
+    trsv_blocked(d.Sf, n, n, xs, Dg, false);
+    trsv_blocked(d.Sf, n, n, xs, Dg, true);   // qc
+    if (tid < B) {
+      double hv = rhs2[n + tid];
+      for (int i = 0; i < n; ++i) hv -= schur[(size_t)i * R + n + tid] * xs[i];
+      sh[tid] = hv;
+    }
+    __syncthreads();
+    if (tid == 0) { small_fwd(sLT, B, sh); small_bwd(sLT, B, sh); }   // w'
+    __syncthreads();
+  }
+  for (int i = tid; i < n; i += nt) {
+    double p = d.pc[i];
+    acc[0] += p * p; acc[1] += gc[i] * p;
+    if (need_phi) { acc[2] += p * xs[i]; acc[3] += rhs2[i] * xs[i]; }
+  }
+  block_sum<4>(acc, sred);
+  if (tid == 0) {
+    double hw = 0;
+    if (need_phi) for (int a = 0; a < B; ++a) hw += rhs2[n + a] * sh[a];
+    out[0] = acc[0] + rhs2[n + B];
+    out[1] = acc[1] + rhs2[n + B + 1];
+    out[2] = need_phi ? acc[2] + rhs2[n + B + 2] - acc[3] - hw : 0.0;
+    out[3] = 0.0;
+  }
+}
+
+// camera part of the step in theta order: internal 6c+{0..2} -> 3c+k, 6c+{3..5} -> 3C+3c+k
+__global__ void k_scatter_cam_step(const double* __restrict__ coef, int C, double* __restrict__ step) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 6 * C) return;
+  int c = i / 6, a = i % 6;
+  step[a < 3 ? 3 * c + a : 3 * C + 3 * c + (a - 3)] = coef[i];
+}
+int bax_scatter_cam_step(bax_handle* h, double* step, cudaStream_t s) {
+  k_scatter_cam_step<<<(6 * h->C + 127) / 128, 128, 0, s>>>(h->coef, h->C, step);
+  BAX_LAUNCH_CHECK();
+  return BAX_OK;
+}
+
+static size_t dense_smem(int n) {
+  size_t d = NBK * LDS_ + ((n + 1) & ~1) + BAX_MAX_B * BAX_MAX_B + BAX_MAX_B + 4 * 32;
+  size_t pn = n > NBK ? (size_t)(n - NBK) * LDS_ : 0;
+  return (d + pn) * sizeof(double);
+}
+
+int bax_dense_solve1(bax_handle* h, cudaStream_t s) {
+  const int n = 6 * h->C;
+  size_t sm = dense_smem(n);
+  if (sm > 227 * 1024) { bax_set_error("reduced camera system of %d unknowns exceeds the single-CTA solver", n); return BAX_E_ARG; }
+  BAX_CUDA(cudaFuncSetAttribute(k_dense_solve1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  BaxTimer t(h, BAX_T_DENSE, s, 1);
+  k_dense_solve1<<<1, DN_THREADS, sm, s>>>(h->buf[BAX_BUF_SCHUR], h->R, h->buf[BAX_BUF_LIN], n, h->B, h->alpha,
+                                           h->dense_ws, h->coef);
+  BAX_LAUNCH_CHECK();
+  return BAX_OK;
+}
+int bax_dense_solve2(bax_handle* h, cudaStream_t s) {
+  const int n = 6 * h->C;
+  size_t sm = dense_smem(n);
+  BAX_CUDA(cudaFuncSetAttribute(k_dense_solve2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  BaxTimer t(h, BAX_T_DENSE, s, 1);
+  k_dense_solve2<<<1, DN_THREADS, sm, s>>>(h->buf[BAX_BUF_SCHUR], h->R, h->buf[BAX_BUF_LIN], n, h->B,
+                                           h->buf[BAX_BUF_RHS2], h->dense_ws, h->need_phi, h->buf[BAX_BUF_STEP]);
+  BAX_LAUNCH_CHECK();
+  return BAX_OK;
+}

@@ -1,0 +1,411 @@
+// Cost, linearisation and the damped Schur-complement trial step.
+#include "bax_internal.cuh"
+
+
+// ------------------------------------------------------------------ cost
+// sum of squared reprojection residuals; grid (nb, C), grid-stride over points of one camera.
+__global__ void __launch_bounds__(256)
+k_cost_reproj(const double* __restrict__ campack, const double* __restrict__ x, const double2* __restrict__ y,
+              const double* __restrict__ s, int64_t P, double* __restrict__ part) {
+  __shared__ double cam[CAMPACK];
+  __shared__ double sm[32];
+  const int c = blockIdx.y;
+  if (threadIdx.x < CAMPACK) cam[threadIdx.x] = campack[(size_t)c * CAMPACK + threadIdx.x];
+  __syncthreads();
+  double acc[1] = {0.0};
+  for (int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x; p < P; p += (int64_t)gridDim.x * 256) {
+    double sc = s[(size_t)c * P + p];
+    if (sc > 0) {
+      double2 yy = y[(size_t)c * P + p];
+      double e0, e1;
+      obs_residual(cam, x[3 * p], x[3 * p + 1], x[3 * p + 2], yy.x, yy.y, sc, e0, e1);
+      acc[0] += e0 * e0 + e1 * e1;
+    }
+  }
+  block_sum<1>(acc, sm);
+  if (threadIdx.x == 0) part[(size_t)blockIdx.y * gridDim.x + blockIdx.x] = acc[0];
+}
+
+// orientation rows: residual^2 sum and (optionally) the transposed Jacobian rows for the SYRK.
+//   r_i = lam1 (1 - |m|),  m = (1/C) sum_c R_c^T d_c
+//   dr_i/drvec_c = -(lam1/C) ((R_c mhat) x d_c)^T Mn_c                      
+// Output element (3c+k, i) at Gv[(3c+k)*sr + i*si]; LM use: Gv [(3C+1)][ldv] (sr=ldv, si=1) with the
+// residual in the last row (rrow); API use: row-major [Nv][3C] (sr=1, si=3C).
+template <bool JAC>
+__global__ void __launch_bounds__(256)
+k_var3d(const double* __restrict__ campack, const double* __restrict__ dhat, int C, int64_t Nv, double lam1,
+        double* __restrict__ Gv, int64_t sr, int64_t si, double* __restrict__ rrow, double* __restrict__ part) {
+  extern __shared__ double sRM[];                 // [C][18]: R, Mn
+  __shared__ double sm[32];
+  for (int i = threadIdx.x; i < 18 * C; i += blockDim.x) {
+    int c = i / 18, k = i % 18;
+    sRM[i] = campack[(size_t)c * CAMPACK + (k < 9 ? 9 + k : 30 + (k - 9))];
+  }
+  __syncthreads();
+  double acc[1] = {0.0};
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < Nv; i += (int64_t)gridDim.x * blockDim.x) {
+    double m0 = 0, m1 = 0, m2 = 0;
+    for (int c = 0; c < C; ++c) {
+      const double* d = dhat + ((size_t)c * Nv + i) * 3;
+      const double* R = sRM + 18 * c;
+      double d0 = d[0], d1 = d[1], d2 = d[2];
+      m0 += R[0] * d0 + R[3] * d1 + R[6] * d2;
+      m1 += R[1] * d0 + R[4] * d1 + R[7] * d2;
+      m2 += R[2] * d0 + R[5] * d1 + R[8] * d2;
+    }
+    m0 /= C; m1 /= C; m2 /= C;
+    double nm = sqrt(m0 * m0 + m1 * m1 + m2 * m2);
+    double r = lam1 * (1.0 - nm);
+    acc[0] += r * r;
+    if (JAC) {
+      double h0 = m0 / nm, h1 = m1 / nm, h2 = m2 / nm, f = -lam1 / C;
+      for (int c = 0; c < C; ++c) {
+        const double* d = dhat + ((size_t)c * Nv + i) * 3;
+        const double* R = sRM + 18 * c; const double* Mn = R + 9;
+        double d0 = d[0], d1 = d[1], d2 = d[2];
+        double a0 = R[0] * h0 + R[1] * h1 + R[2] * h2;      // R mhat
+        double a1 = R[3] * h0 + R[4] * h1 + R[5] * h2;
+        double a2 = R[6] * h0 + R[7] * h1 + R[8] * h2;
+        double c0 = a1 * d2 - a2 * d1, c1 = a2 * d0 - a0 * d2, c2 = a0 * d1 - a1 * d0;
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+          Gv[(size_t)(3 * c + k) * sr + (size_t)i * si] = f * (c0 * Mn[k] + c1 * Mn[3 + k] + c2 * Mn[6 + k]);
+      }
+      if (rrow) rrow[i] = r;
+    }
+  }
+  block_sum<1>(acc, sm);
+  if (threadIdx.x == 0) part[blockIdx.x] = acc[0];
+}
+
+static int obs_grid(bax_handle* h) {            // blocks per camera for grid-stride kernels
+  int g = h->nblk_obs;
+  int cap = (8 * h->sm_count + h->C - 1) / h->C;
+  if (cap < 1) cap = 1;
+  return g < cap ? g : cap;
+}
+static int row_grid(bax_handle* h, int64_t n) {
+  int64_t g = (n + 255) / 256; int cap = 8 * h->sm_count;
+  return (int)(g < cap ? (g > 0 ? g : 1) : cap);
+}
+
+extern "C" int bax_cost_begin(bax_handle* h, const double* theta, void* stream) {
+  if (!h || !h->campack || !theta) { bax_set_error("bax_cost_begin: bad argument / no problem"); return BAX_E_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  BAX_CUDA(cudaSetDevice(h->device));
+  BaxTimer t(h, BAX_T_COST, s, 4);
+  int rc = bax_launch_cam_prep(h, theta, s); if (rc) return rc;
+  return bax_bone_pass1(h, theta, s);
+}
+extern "C" int bax_cost_mid(bax_handle* h, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  BaxTimer t(h, BAX_T_COST, s, 6);
+  double* out = h->buf[BAX_BUF_COST];
+  int rc = bax_bone_pass2(h, h->theta, out, s); if (rc) return rc;
+  int g = obs_grid(h);
+  double* part = h->partials;
+  k_cost_reproj<<<dim3(g, h->C), 256, 0, s>>>(h->campack, h->theta + 6 * h->C, (const double2*)h->y2d, h->s2d, h->P, part);
+  BAX_LAUNCH_CHECK();
+  rc = bax_reduce_partials(h, part, g * h->C, 1, out + h->B, s); if (rc) return rc;
+  if (h->Nv > 0) {
+    int gv = row_grid(h, h->Nv);
+    double* part2 = h->partials + (1 << 20);
+    k_var3d<false><<<gv, 256, 18 * h->C * sizeof(double), s>>>(h->campack, h->dhat, h->C, h->Nv, h->lam1, nullptr, 0, 0, nullptr, part2);
+    BAX_LAUNCH_CHECK();
+    rc = bax_reduce_partials(h, part2, gv, 1, out + h->B + 1, s); if (rc) return rc;
+  } else {
+    BAX_CUDA(cudaMemsetAsync(out + h->B + 1, 0, sizeof(double), s));
+  }
+  return BAX_OK;
+}
+static double bone_cost_host(bax_handle* h, const double* ssq, double count) {
+  double c = 0;
+  for (int b = 0; b < h->B; ++b) { double r = h->lam2 * ssq[b] / count; c += r * r; }
+  return c;
+}
+extern "C" int bax_cost_finish(bax_handle* h, double* cost_host, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  double* hp = h->host_pinned;
+  BAX_CUDA(cudaMemcpyAsync(hp, h->buf[BAX_BUF_COST], sizeof(double) * (h->B + 2), cudaMemcpyDeviceToHost, s));
+  BAX_CUDA(cudaMemcpyAsync(hp + 32, h->buf[BAX_BUF_BONE] + h->B, sizeof(double), cudaMemcpyDeviceToHost, s));
+  BAX_CUDA(cudaStreamSynchronize(s));
+  *cost_host = 0.5 * (hp[h->B] + hp[h->B + 1] + bone_cost_host(h, hp, hp[32]));
+  return BAX_OK;
+}
+
+// ------------------------------------------------------------------ linearisation
+// per-camera 6x6 block sum_p Jc^T Jc (21 unique), gradient Jc^T e (6), sum e^2 (1).
+__global__ void __launch_bounds__(256)
+k_lin_cam(const double* __restrict__ campack, const double* __restrict__ x, const double2* __restrict__ y,
+          const double* __restrict__ s, int64_t P, int C, double* __restrict__ part /*[gridDim.x][C][28]*/) {
+  __shared__ double cam[CAMPACK];
+  __shared__ double sm[28 * 32];
+  const int c = blockIdx.y;
+  if (threadIdx.x < CAMPACK) cam[threadIdx.x] = campack[(size_t)c * CAMPACK + threadIdx.x];
+  __syncthreads();
+  double acc[28];
+#pragma unroll
+  for (int i = 0; i < 28; ++i) acc[i] = 0.0;
+  for (int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x; p < P; p += (int64_t)gridDim.x * 256) {
+    double sc = s[(size_t)c * P + p];
+    if (sc > 0) {
+      double2 yy = y[(size_t)c * P + p];
+      ObsLin o;
+      obs_linearize<true>(cam, x[3 * p], x[3 * p + 1], x[3 * p + 2], yy.x, yy.y, sc, o);
+      double j0[6] = {o.jr[0][0], o.jr[0][1], o.jr[0][2], o.jt[0][0], o.jt[0][1], o.jt[0][2]};
+      double j1[6] = {o.jr[1][0], o.jr[1][1], o.jr[1][2], o.jt[1][0], o.jt[1][1], o.jt[1][2]};
+      int k = 0;
+#pragma unroll
+      for (int a = 0; a < 6; ++a) {
+#pragma unroll
+        for (int b = a; b < 6; ++b) { acc[k] += j0[a] * j0[b] + j1[a] * j1[b]; ++k; }
+      }
+#pragma unroll
+      for (int a = 0; a < 6; ++a) acc[21 + a] += j0[a] * o.e0 + j1[a] * o.e1;
+      acc[27] += o.e0 * o.e0 + o.e1 * o.e1;
+    }
+  }
+  block_sum<28>(acc, sm);
+  if (threadIdx.x == 0) {
+    double* o = part + ((size_t)blockIdx.x * C + c) * 28;
+    for (int i = 0; i < 28; ++i) o[i] = acc[i];
+  }
+}
+
+// per-point 3x3 block V_p = sum_c Jp^T Jp and reprojection gradient g_p = sum_c Jp^T e.
+__global__ void __launch_bounds__(128)
+k_lin_pt(const double* __restrict__ campack, const double* __restrict__ x, const double2* __restrict__ y,
+         const double* __restrict__ s, int64_t P, int C, double* __restrict__ Vp, double* __restrict__ gp) {
+  extern __shared__ double cams[];               // [C][CAMPACK]
+  for (int i = threadIdx.x; i < C * CAMPACK; i += blockDim.x) cams[i] = campack[i];
+  __syncthreads();
+  int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  double x0 = x[3 * p], x1 = x[3 * p + 1], x2 = x[3 * p + 2];
+  double V[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
+  for (int c = 0; c < C; ++c) {
+    double sc = s[(size_t)c * P + p];
+    if (sc > 0) {
+      double2 yy = y[(size_t)c * P + p];
+      ObsLin o;
+      obs_linearize<false>(cams + c * CAMPACK, x0, x1, x2, yy.x, yy.y, sc, o);
+      V[0] += o.jp[0][0] * o.jp[0][0] + o.jp[1][0] * o.jp[1][0];
+      V[1] += o.jp[0][0] * o.jp[0][1] + o.jp[1][0] * o.jp[1][1];
+      V[2] += o.jp[0][0] * o.jp[0][2] + o.jp[1][0] * o.jp[1][2];
+      V[3] += o.jp[0][1] * o.jp[0][1] + o.jp[1][1] * o.jp[1][1];
+      V[4] += o.jp[0][1] * o.jp[0][2] + o.jp[1][1] * o.jp[1][2];
+      V[5] += o.jp[0][2] * o.jp[0][2] + o.jp[1][2] * o.jp[1][2];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) g[k] += o.jp[0][k] * o.e0 + o.jp[1][k] * o.e1;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 6; ++k) Vp[6 * p + k] = V[k];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) gp[3 * p + k] = g[k];
+}
+
+// scatter the per-camera sums and the orientation-row SYRK into the packed LIN buffer
+//   lin = [ Hcc (6C x 6C) | gc (6C) | ssq_b (B) | sum e^2 | sum r_v3d^2 ]
+__global__ void k_lin_pack(const double* __restrict__ camsum /*[C][28]*/, const double* __restrict__ v3d /*[(3C+1)^2] or null*/,
+                           int C, double* __restrict__ lin, int B) {
+  const int C6 = 6 * C, n3 = 3 * C + 1;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < C6 * C6; idx += gridDim.x * blockDim.x) {
+    int i = idx / C6, j = idx % C6;
+    int ci = i / 6, a = i % 6, cj = j / 6, b = j % 6;
+    double v = 0.0;
+    if (ci == cj) {
+      int lo = a < b ? a : b, hi = a < b ? b : a;
+      int k = lo * 6 - lo * (lo - 1) / 2 + (hi - lo);
+      v = camsum[ci * 28 + k];
+    }
+    if (v3d && a < 3 && b < 3) v += v3d[(size_t)(3 * ci + a) * n3 + (3 * cj + b)];
+    lin[idx] = v;
+  }
+  if (blockIdx.x == 0) {
+    double* gc = lin + (size_t)C6 * C6;
+    for (int i = threadIdx.x; i < C6; i += blockDim.x) {
+      int c = i / 6, a = i % 6;
+      double v = camsum[c * 28 + 21 + a];
+      if (v3d && a < 3) v += v3d[(size_t)(3 * c + a) * n3 + 3 * C];
+      gc[i] = v;
+    }
+    if (threadIdx.x == 0) {
+      double e = 0; for (int c = 0; c < C; ++c) e += camsum[c * 28 + 27];
+      gc[C6 + B] = e;
+      gc[C6 + B + 1] = v3d ? v3d[(size_t)(3 * C) * n3 + 3 * C] : 0.0;
+    }
+  }
+}
+
+// after the LIN reduction: Lbar_b, r_b = lam2 * ssq_b / Ntot
+__global__ void k_bone_finalize(const double* __restrict__ bone_buf, const double* __restrict__ ssq, int B,
+                                double lam2, double* __restrict__ Lbar, double* __restrict__ rb) {
+  int b = threadIdx.x;
+  if (b < B) { Lbar[b] = bone_buf[b] / bone_buf[B]; rb[b] = lam2 * ssq[b] / bone_buf[B]; }
+}
+
+// bone-length Jacobian entry of point p for incident bone (b, sgn):  u = sgn * lam2 (2/Ntot) (L - Lbar) dv / L
+__device__ __forceinline__ void bone_u(const double* __restrict__ x, int64_t frame_base3, const int32_t* __restrict__ bones,
+                                       int b, int sgn, const double* __restrict__ Lbar, double scale, double (&u)[3]) {
+  const double* a = x + frame_base3 + 3 * bones[2 * b];
+  const double* q = x + frame_base3 + 3 * bones[2 * b + 1];
+  double d0 = a[0] - q[0], d1 = a[1] - q[1], d2 = a[2] - q[2];
+  double L = sqrt(d0 * d0 + d1 * d1 + d2 * d2);
+  double f = sgn * scale * (L - Lbar[b]) / L;
+  u[0] = f * d0; u[1] = f * d1; u[2] = f * d2;
+}
+
+// g_p += sum_b u_pb r_b; partial sums of |g_p|^2, |x_p|^2 and max |g_p|.
+__global__ void __launch_bounds__(256)
+k_gp_bone(const double* __restrict__ x, int64_t P, int J, const int32_t* __restrict__ bones,
+          const int32_t* __restrict__ joint_bones, const double* __restrict__ Lbar, const double* __restrict__ rb,
+          double scale, double* __restrict__ gp, double* __restrict__ part /*[grid][2]*/, double* __restrict__ pmax) {
+  __shared__ double sm[2 * 32];
+  __shared__ double smax[8];
+  double acc[2] = {0, 0}, mx = 0;
+  for (int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x; p < P; p += (int64_t)gridDim.x * 256) {
+    int j = (int)(p % J); int64_t fb = (p - j) * 3;
+    double g0 = gp[3 * p], g1 = gp[3 * p + 1], g2 = gp[3 * p + 2];
+#pragma unroll
+    for (int k = 0; k < BAX_MAX_JB; ++k) {
+      int b = joint_bones[(j * BAX_MAX_JB + k) * 2];
+      if (b >= 0) {
+        double u[3];
+        bone_u(x, fb, bones, b, joint_bones[(j * BAX_MAX_JB + k) * 2 + 1], Lbar, scale, u);
+        double r = rb[b];
+        g0 += u[0] * r; g1 += u[1] * r; g2 += u[2] * r;
+      }
+    }
+    gp[3 * p] = g0; gp[3 * p + 1] = g1; gp[3 * p + 2] = g2;
+    acc[0] += g0 * g0 + g1 * g1 + g2 * g2;
+    acc[1] += x[3 * p] * x[3 * p] + x[3 * p + 1] * x[3 * p + 1] + x[3 * p + 2] * x[3 * p + 2];
+    mx = fmax(mx, fmax(fabs(g0), fmax(fabs(g1), fabs(g2))));
+  }
+  for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = mx;
+  block_sum<2>(acc, sm);
+  if (threadIdx.x == 0) {
+    for (int w = 0; w < 8; ++w) mx = fmax(mx, smax[w]);
+    part[2 * blockIdx.x] = acc[0]; part[2 * blockIdx.x + 1] = acc[1];
+    pmax[blockIdx.x] = mx;
+  }
+}
+__global__ void k_reduce_max(const double* __restrict__ v, int n, double* __restrict__ out) {
+  __shared__ double sm[32];
+  double mx = 0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) mx = fmax(mx, v[i]);
+  for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = mx;
+  __syncthreads();
+  if (threadIdx.x == 0) { for (int w = 0; w < (int)(blockDim.x >> 5); ++w) mx = fmax(mx, sm[w]); *out = mx; }
+}
+
+static int ensure_trial_buffers(bax_handle* h) {
+  if (!h->Yhat) {
+    BAX_CUDA(cudaMalloc(&h->Yhat, sizeof(double) * (size_t)h->R * h->ldy));
+    BAX_CUDA(cudaMemset(h->Yhat, 0, sizeof(double) * (size_t)h->R * h->ldy));
+  }
+  if (!h->Gv && h->Nv > 0) {
+    BAX_CUDA(cudaMalloc(&h->Gv, sizeof(double) * (size_t)(3 * h->C + 1) * h->ldv));
+    BAX_CUDA(cudaMemset(h->Gv, 0, sizeof(double) * (size_t)(3 * h->C + 1) * h->ldv));
+  }
+  return BAX_OK;
+}
+
+extern "C" int bax_linearize_begin(bax_handle* h, const double* theta, void* stream) {
+  if (!h || !h->campack || !theta) { bax_set_error("bax_linearize_begin: bad argument / no problem"); return BAX_E_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  BAX_CUDA(cudaSetDevice(h->device));
+  int rc = ensure_trial_buffers(h); if (rc) return rc;
+  BaxTimer t(h, BAX_T_LIN, s, 4);
+  rc = bax_launch_cam_prep(h, theta, s, true); if (rc) return rc;
+  return bax_bone_pass1(h, theta, s);
+}
+
+extern "C" int bax_linearize_mid(bax_handle* h, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  const int C = h->C, C6 = 6 * C;
+  const double* x = h->theta_lin + C6;
+  double* lin = h->buf[BAX_BUF_LIN];
+  int rc;
+  {
+    BaxTimer t(h, BAX_T_LIN, s, 6);
+    int g = obs_grid(h);
+    double* part = h->partials;                  // [g][C][28]
+    if ((size_t)g * C * 28 * sizeof(double) > h->partials_bytes / 4) { bax_set_error("partials overflow"); return BAX_E_STATE; }
+    k_lin_cam<<<dim3(g, C), 256, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
+    BAX_LAUNCH_CHECK();
+    double* camsum = h->partials + (1 << 20);    // [C][28]
+    rc = bax_reduce_partials(h, part, g, C * 28, camsum, s); if (rc) return rc;
+    int nbp = (int)((h->P + 127) / 128);
+    k_lin_pt<<<nbp, 128, C * CAMPACK * sizeof(double), s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, h->Vp, h->gp);
+    BAX_LAUNCH_CHECK();
+    rc = bax_bone_pass2(h, h->theta_lin, lin + (size_t)C6 * C6 + C6, s); if (rc) return rc;
+  }
+  double* v3d = nullptr;
+  if (h->Nv > 0) {
+    int gv = row_grid(h, h->Nv);
+    {
+      BaxTimer t(h, BAX_T_LIN, s, 1);
+      k_var3d<true><<<gv, 256, 18 * C * sizeof(double), s>>>(h->campack_lin, h->dhat, C, h->Nv, h->lam1, h->Gv, h->ldv, 1,
+                                                               h->Gv + (size_t)(3 * C) * h->ldv, h->partials + (1 << 20) + 4096);
+      BAX_LAUNCH_CHECK();
+    }
+    v3d = h->partials + (1 << 20) + 8192 + 65536;       // [(3C+1)^2]
+    rc = bax_syrk(h, h->Gv, 3 * C + 1, h->Nv, h->ldv, v3d, s); if (rc) return rc;
+  }
+  k_lin_pack<<<64, 256, 0, s>>>(h->partials + (1 << 20), v3d, C, lin, h->B);
+  BAX_LAUNCH_CHECK();
+  return BAX_OK;
+}
+
+// after the LIN all-reduce: finish g_p with the bone-length rows, start the norm reductions
+extern "C" int bax_linearize_post(bax_handle* h, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  const int C6 = 6 * h->C;
+  BaxTimer t(h, BAX_T_LIN, s, 4);
+  double* lin = h->buf[BAX_BUF_LIN];
+  k_bone_finalize<<<1, 32, 0, s>>>(h->buf[BAX_BUF_BONE], lin + (size_t)C6 * C6 + C6, h->B, h->lam2, h->Lbar, h->rb);
+  BAX_LAUNCH_CHECK();
+  int g = row_grid(h, h->P);
+  double* part = h->partials; double* pmax = h->partials + (1 << 16);
+  // scale = lam2 * 2 / Ntot ; Ntot lives on device (buf[BONE][B]); single-GPU fast path reads host N,
+  // multi-GPU callers set it through bax_set_global_frames before linearising.
+  double scale = h->lam2 * 2.0 / (double)h->n_frames_global;
+  k_gp_bone<<<g, 256, 0, s>>>(h->theta_lin + C6, h->P, h->J, h->bones, h->joint_bones, h->Lbar, h->rb, scale, h->gp, part, pmax);
+  BAX_LAUNCH_CHECK();
+  int rc = bax_reduce_partials(h, part, g, 2, h->buf[BAX_BUF_NORM], s); if (rc) return rc;
+  k_reduce_max<<<1, 256, 0, s>>>(pmax, g, h->buf[BAX_BUF_GMAX]);
+  BAX_LAUNCH_CHECK();
+  return BAX_OK;
+}
+
+extern "C" int bax_linearize_finish(bax_handle* h, double* out_host, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  const int C6 = 6 * h->C, B = h->B;
+  if (C6 + B + 2 + 8 + C6 > 4096) { bax_set_error("too many cameras for the scalar staging buffer"); return BAX_E_ARG; }
+  static thread_local double stage[4096];
+  double* lin = h->buf[BAX_BUF_LIN];
+  BAX_CUDA(cudaMemcpyAsync(stage, lin + (size_t)C6 * C6, sizeof(double) * (C6 + B + 2), cudaMemcpyDeviceToHost, s));
+  BAX_CUDA(cudaMemcpyAsync(stage + C6 + B + 2, h->buf[BAX_BUF_NORM], sizeof(double) * 2, cudaMemcpyDeviceToHost, s));
+  BAX_CUDA(cudaMemcpyAsync(stage + C6 + B + 4, h->buf[BAX_BUF_GMAX], sizeof(double), cudaMemcpyDeviceToHost, s));
+  BAX_CUDA(cudaMemcpyAsync(stage + C6 + B + 5, h->buf[BAX_BUF_BONE] + B, sizeof(double), cudaMemcpyDeviceToHost, s));
+  BAX_CUDA(cudaMemcpyAsync(stage + C6 + B + 8, h->theta_lin, sizeof(double) * C6, cudaMemcpyDeviceToHost, s));
+  BAX_CUDA(cudaStreamSynchronize(s));
+  const double* gc = stage; const double* ssq = stage + C6;
+  double ginf = stage[C6 + B + 4], g2 = stage[C6 + B + 2], x2 = stage[C6 + B + 3];
+  for (int i = 0; i < C6; ++i) { ginf = fmax(ginf, fabs(gc[i])); g2 += gc[i] * gc[i]; x2 += stage[C6 + B + 8 + i] * stage[C6 + B + 8 + i]; }
+  h->cost = 0.5 * (stage[C6 + B] + stage[C6 + B + 1] + bone_cost_host(h, ssq, stage[C6 + B + 5]));
+  out_host[0] = h->cost; out_host[1] = ginf; out_host[2] = sqrt(g2); out_host[3] = sqrt(x2);
+  return BAX_OK;
+}
+
+// orientation-row Jacobian in row-major [Nv][3C] for bax_prior_jacobian
+int bax_var3d_jacobian_rowmajor(bax_handle* h, double* Jv3d, cudaStream_t s) {
+  int gv = row_grid(h, h->Nv);
+  k_var3d<true><<<gv, 256, 18 * h->C * sizeof(double), s>>>(h->campack, h->dhat, h->C, h->Nv, h->lam1, Jv3d, 1,
+                                                             3 * h->C, nullptr, h->partials + (1 << 20) + 4096);
+  BAX_LAUNCH_CHECK();
+  return BAX_OK;
+}

@@ -1,0 +1,217 @@
+// Residual vector (ba.objfun) and the fused residual + Jacobian kernel (one thread per observation).
+#include "bax_internal.cuh"
+
+// ------------------------------------------------------------------ compaction helper
+// Rank of this thread's visible observation inside its 256-thread block (reference row order is
+// camera-major, visible only: ba.py:44-61), by warp ballots + a 8-entry shared scan.
+__device__ __forceinline__ int block_rank(bool vis, int* s_warp /*[8]*/) {
+  unsigned m = __ballot_sync(0xffffffffu, vis);
+  int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int r = __popc(m & ((1u << lane) - 1u));
+  if (lane == 0) s_warp[warp] = __popc(m);
+  __syncthreads();
+  int base = 0;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) base += (w < warp) ? s_warp[w] : 0;
+  return base + r;
+}
+
+// ------------------------------------------------------------------ reprojection rows
+__global__ void __launch_bounds__(256)
+k_residual_reproj(const double* __restrict__ campack, const double* __restrict__ x,
+                  const double2* __restrict__ y, const double* __restrict__ s, int64_t P,
+                  const int64_t* __restrict__ blockbase, double* __restrict__ r_out) {
+  __shared__ double cam[CAMPACK];
+  __shared__ int s_warp[8];
+  const int c = blockIdx.y;
+  if (threadIdx.x < CAMPACK) cam[threadIdx.x] = campack[(size_t)c * CAMPACK + threadIdx.x];
+  const int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  double sc = 0.0; double2 yy = make_double2(0, 0);
+  if (p < P) { sc = s[(size_t)c * P + p]; yy = y[(size_t)c * P + p]; }
+  const bool vis = sc > 0;                       // NaN score -> not visible, as (ss2d > 0) in ba.py:124
+  int rank = block_rank(vis, s_warp);            // contains the __syncthreads that publishes cam[]
+  if (!vis) return;
+  double e0, e1;
+  obs_residual(cam, x[3 * p], x[3 * p + 1], x[3 * p + 2], yy.x, yy.y, sc, e0, e1);
+  int64_t row = blockbase[(size_t)c * gridDim.x + blockIdx.x] + rank;
+  reinterpret_cast<double2*>(r_out)[row] = make_double2(e0, e1);
+}
+
+// Fused residual + Jacobian blocks, materialised (the HBM-bound kernel of SURVEY §8d):
+// algorithmic bytes per visible observation: read y 16 + s 8 + x 24/Cbar, write r 16 + Jcam 96 + Jpt 48.
+// Output staging: each warp transposes its blocks through shared memory so every global store
+// instruction writes 32 consecutive 16-byte words (full 128-byte lines).
+__global__ void __launch_bounds__(256)
+k_rj(const double* __restrict__ campack, const double* __restrict__ x, const double2* __restrict__ y,
+     const double* __restrict__ s, int64_t P, const int64_t* __restrict__ blockbase,
+     double2* __restrict__ r2, double2* __restrict__ Jcam, double2* __restrict__ Jpt,
+     int32_t* __restrict__ obs_cam, int32_t* __restrict__ obs_pt) {
+  __shared__ double cam[CAMPACK];
+  __shared__ int s_warp[8];
+  __shared__ double2 stage[8][32 * 9 + 1];       // per warp: 32 observations x 9 double2 (6 Jcam + 3 Jpt)
+  const int c = blockIdx.y;
+  if (threadIdx.x < CAMPACK) cam[threadIdx.x] = campack[(size_t)c * CAMPACK + threadIdx.x];
+  const int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  double sc = 0.0; double2 yy = make_double2(0, 0);
+  if (p < P) { sc = s[(size_t)c * P + p]; yy = y[(size_t)c * P + p]; }
+  const bool vis = sc > 0;
+  const unsigned bal = __ballot_sync(0xffffffffu, vis);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int wr = __popc(bal & ((1u << lane) - 1u));
+  if (lane == 0) s_warp[warp] = __popc(bal);
+  __syncthreads();
+  int wbase = 0;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) wbase += (w < warp) ? s_warp[w] : 0;
+  const int nw = s_warp[warp];
+  const int64_t row0 = blockbase[(size_t)c * gridDim.x + blockIdx.x] + wbase;   // first row of this warp
+  if (vis) {
+    ObsLin o;
+    obs_linearize<true>(cam, x[3 * p], x[3 * p + 1], x[3 * p + 2], yy.x, yy.y, sc, o);
+    r2[row0 + wr] = make_double2(o.e0, o.e1);
+    if (obs_cam) { obs_cam[row0 + wr] = c; obs_pt[row0 + wr] = (int32_t)p; }
+    double2* st = &stage[warp][wr * 9];
+    st[0] = make_double2(o.jr[0][0], o.jr[0][1]);
+    st[1] = make_double2(o.jr[0][2], o.jt[0][0]);
+    st[2] = make_double2(o.jt[0][1], o.jt[0][2]);
+    st[3] = make_double2(o.jr[1][0], o.jr[1][1]);
+    st[4] = make_double2(o.jr[1][2], o.jt[1][0]);
+    st[5] = make_double2(o.jt[1][1], o.jt[1][2]);
+    st[6] = make_double2(o.jp[0][0], o.jp[0][1]);
+    st[7] = make_double2(o.jp[0][2], o.jp[1][0]);
+    st[8] = make_double2(o.jp[1][1], o.jp[1][2]);
+  }
+  __syncwarp();
+  // coalesced write-out: Jcam rows row0..row0+nw-1 are 6*nw consecutive double2, Jpt 3*nw
+  double2* jc = Jcam + row0 * 6;
+  for (int i = lane; i < 6 * nw; i += 32) jc[i] = stage[warp][(i / 6) * 9 + (i % 6)];
+  double2* jq = Jpt + row0 * 3;
+  for (int i = lane; i < 3 * nw; i += 32) jq[i] = stage[warp][(i / 3) * 9 + 6 + (i % 3)];
+}
+
+// ------------------------------------------------------------------ orientation rows  (ba.py:67-96)
+__global__ void k_var3d_residual(const double* __restrict__ campack, const double* __restrict__ dhat,
+                                 int C, int64_t Nv, double lam1, double* __restrict__ r_out) {
+  extern __shared__ double sR[];                 // [C][9]
+  for (int i = threadIdx.x; i < 9 * C; i += blockDim.x) sR[i] = campack[(size_t)(i / 9) * CAMPACK + 9 + (i % 9)];
+  __syncthreads();
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Nv) return;
+  double m0 = 0, m1 = 0, m2 = 0;
+  for (int c = 0; c < C; ++c) {
+    const double* d = dhat + ((size_t)c * Nv + i) * 3;
+    const double* R = sR + 9 * c;
+    double d0 = d[0], d1 = d[1], d2 = d[2];
+    m0 += R[0] * d0 + R[3] * d1 + R[6] * d2;     // R^T d
+    m1 += R[1] * d0 + R[4] * d1 + R[7] * d2;
+    m2 += R[2] * d0 + R[5] * d1 + R[8] * d2;
+  }
+  m0 /= C; m1 /= C; m2 /= C;
+  r_out[i] = lam1 * (1.0 - sqrt(m0 * m0 + m1 * m1 + m2 * m2));
+}
+
+// ------------------------------------------------------------------ bone-length rows  (ba.py:99-110)
+// pass 1: per-bone sum of lengths over the local frames; pass 2: sum of squared deviations from
+// the (global) mean.  Two passes keep the population variance accurate to FP64 round-off.
+__global__ void __launch_bounds__(256)
+k_bone_len(const double* __restrict__ x, int N, int J, int B, const int32_t* __restrict__ bones,
+           const double* __restrict__ bone_buf /* null in pass 1: [B] sums, [B] = count */,
+           double* __restrict__ part /*[gridDim.x][BAX_MAX_B]*/) {
+  __shared__ double sm[BAX_MAX_B * 32];
+  double acc[BAX_MAX_B];
+#pragma unroll
+  for (int b = 0; b < BAX_MAX_B; ++b) acc[b] = 0.0;
+  for (int n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x) {
+    const double* xf = x + (size_t)n * J * 3;
+#pragma unroll
+    for (int b = 0; b < BAX_MAX_B; ++b) {
+      if (b < B) {
+        const double* a = xf + 3 * bones[2 * b];
+        const double* q = xf + 3 * bones[2 * b + 1];
+        double d0 = a[0] - q[0], d1 = a[1] - q[1], d2 = a[2] - q[2];
+        double L = sqrt(d0 * d0 + d1 * d1 + d2 * d2);
+        if (bone_buf) { double dl = L - bone_buf[b] / bone_buf[B]; acc[b] += dl * dl; }
+        else acc[b] += L;
+      }
+    }
+  }
+  block_sum<BAX_MAX_B>(acc, sm);
+  if (threadIdx.x == 0)
+    for (int b = 0; b < BAX_MAX_B; ++b) part[(size_t)blockIdx.x * BAX_MAX_B + b] = acc[b];
+}
+__global__ void k_set_scalar(double* p, double v) { *p = v; }
+__global__ void k_bone_rows(const double* __restrict__ ssq, const double* __restrict__ bone_buf, int B,
+                            double lam2, double* __restrict__ r_out) {
+  int b = threadIdx.x;
+  if (b < B) r_out[b] = lam2 * ssq[b] / bone_buf[B];
+}
+
+static int bone_grid(bax_handle* h) {
+  int g = (h->N + 255) / 256;
+  int cap = 4 * h->sm_count;
+  return g < cap ? g : cap;
+}
+// fills buf[BONE] = { sum_n L_nb (b < B), local frame count }
+int bax_bone_pass1(bax_handle* h, const double* theta, cudaStream_t s) {
+  int g = bone_grid(h);
+  const double* x = theta + 6 * h->C;
+  k_bone_len<<<g, 256, 0, s>>>(x, h->N, h->J, h->B, h->bones, nullptr, h->partials);
+  BAX_LAUNCH_CHECK();
+  if (h->B > 0) { int rc = bax_reduce_partials(h, h->partials, g, h->B, h->buf[BAX_BUF_BONE], s); if (rc) return rc; }
+  k_set_scalar<<<1, 1, 0, s>>>(h->buf[BAX_BUF_BONE] + h->B, (double)h->N);
+  BAX_LAUNCH_CHECK();
+  return BAX_OK;
+}
+// out[b] = sum_n (L_nb - Lbar_b)^2 over local frames (Lbar from the, possibly all-reduced, buf[BONE])
+int bax_bone_pass2(bax_handle* h, const double* theta, double* out, cudaStream_t s) {
+  if (h->B == 0) return BAX_OK;
+  int g = bone_grid(h);
+  const double* x = theta + 6 * h->C;
+  double* part = h->partials + (size_t)(1 << 21);     // second half: pass-1 partials may still be live
+  k_bone_len<<<g, 256, 0, s>>>(x, h->N, h->J, h->B, h->bones, h->buf[BAX_BUF_BONE], part);
+  BAX_LAUNCH_CHECK();
+  return bax_reduce_partials(h, part, g, h->B, out, s);
+}
+
+// ------------------------------------------------------------------ API
+extern "C" int bax_residual(bax_handle* h, const double* theta, double* r_out, void* stream) {
+  if (!h || !h->campack || !theta || !r_out) { bax_set_error("bax_residual: bad argument / no problem"); return BAX_E_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  BAX_CUDA(cudaSetDevice(h->device));
+  int rc = bax_launch_cam_prep(h, theta, s); if (rc) return rc;
+  const double* x = theta + 6 * h->C;
+  k_residual_reproj<<<dim3(h->nblk_obs, h->C), 256, 0, s>>>(h->campack, x, (const double2*)h->y2d, h->s2d,
+                                                            h->P, h->blockbase, r_out);
+  BAX_LAUNCH_CHECK();
+  if (h->Nv > 0) {
+    k_var3d_residual<<<(unsigned)((h->Nv + 255) / 256), 256, 9 * h->C * sizeof(double), s>>>(
+        h->campack, h->dhat, h->C, h->Nv, h->lam1, r_out + 2 * h->n_vis);
+    BAX_LAUNCH_CHECK();
+  }
+  if (h->B > 0) {
+    rc = bax_bone_pass1(h, theta, s); if (rc) return rc;
+    rc = bax_bone_pass2(h, theta, h->buf[BAX_BUF_COST], s); if (rc) return rc;
+    k_bone_rows<<<1, 32, 0, s>>>(h->buf[BAX_BUF_COST], h->buf[BAX_BUF_BONE], h->B, h->lam2,
+                                 r_out + 2 * h->n_vis + h->Nv);
+    BAX_LAUNCH_CHECK();
+  }
+  return BAX_OK;
+}
+
+extern "C" int bax_residual_jacobian(bax_handle* h, const double* theta, double* r2, double* Jcam, double* Jpt,
+                                     int32_t* obs_cam, int32_t* obs_pt, void* stream) {
+  if (!h || !h->campack || !theta || !r2 || !Jcam || !Jpt || ((obs_cam == nullptr) != (obs_pt == nullptr))) {
+    bax_set_error("bax_residual_jacobian: bad argument / no problem"); return BAX_E_ARG;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  BAX_CUDA(cudaSetDevice(h->device));
+  int rc = bax_launch_cam_prep(h, theta, s); if (rc) return rc;
+  {
+    BaxTimer t(h, BAX_T_RJ, s, 1);
+    k_rj<<<dim3(h->nblk_obs, h->C), 256, 0, s>>>(h->campack, theta + 6 * h->C, (const double2*)h->y2d, h->s2d,
+                                                 h->P, h->blockbase, (double2*)r2, (double2*)Jcam, (double2*)Jpt,
+                                                 obs_cam, obs_pt);
+  }
+  BAX_LAUNCH_CHECK();
+  return BAX_OK;
+}

@@ -1,0 +1,113 @@
+/* bax.h — C ABI of the B200-native bundle-adjustment hot path (libbax.so).
+ *
+ * The reference (pure Python) has no FFI; its boundary for this path is the set of Python
+ * functions in ba.py and util.py.  Each entry point below names the reference lines it
+ * replaces.  All array arguments are CUDA DEVICE pointers unless marked "host"; every call
+ * is ordered on the given cudaStream_t (passed as void*; 0 = legacy default stream), returns
+ * 0 on success and a negative code on failure (bax_last_error() gives the thread-local text).
+ * No exception crosses the ABI.  One handle per device; calls on a handle are not re-entrant.
+ *
+ * Parameter vector theta (reference ba.py:18-31):  [ rvec_0..rvec_{C-1} | t_0..t_{C-1} | x_0..x_{P-1} ],
+ * P = N*J points, n = 6C + 3P.  Residual rows (reference ba.py:113-140): camera-major visible
+ * reprojection rows (ex,ey interleaved), then lambda1 * orientation rows, then lambda2 * B
+ * bone-length-variance rows.
+ */
+#ifndef BAX_H
+#define BAX_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct bax_handle bax_handle;
+
+enum { BAX_OK = 0, BAX_E_ARG = -1, BAX_E_CUDA = -2, BAX_E_STATE = -3, BAX_E_NUMERIC = -4 };
+
+const char* bax_last_error(void);
+int bax_version(void);
+
+int bax_create(int device, bax_handle** out);
+int bax_destroy(bax_handle* h);
+
+/* Bind one BA problem (replaces the argument tuple of ba.objfun, reference ba.py:113 and
+ * ba_main ba.py:157-206).  y2d [C][N*J][2], s2d [C][N*J] are referenced, not copied (caller keeps
+ * them alive); p3d [C][N][J3][3], s3d [C][N][J3] are consumed here: the constant unit bone
+ * directions of the orientation term and their valid-row compaction (ba.py:73-91) are derived
+ * once.  bones: host int32 [B][2] (util.OP_BONE, util.py:129-145); it indexes the J axis for the
+ * bone-length term and the J3 axis for the orientation term, as the reference does. */
+int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B,
+                    const double* K, const double* y2d, const double* s2d,
+                    const double* p3d, const double* s3d, const int32_t* bones_host,
+                    double lambda1, double lambda2, void* stream);
+
+/* dims_host[0..5] = { n_vis (visible observations), n_v3d (valid orientation rows),
+ *                     m (residual rows), n (parameters), aug_rows (6C+13), n_points } */
+int bax_problem_dims(bax_handle* h, int64_t* dims_host);
+
+/* r_out[m] = ba.objfun(theta, ...)  (reference ba.py:113-140: objfun_nll 34-63,
+ * objfun_var3d 67-96, objfun_varbone 99-110). */
+int bax_residual(bax_handle* h, const double* theta, double* r_out, void* stream);
+
+/* Fused residual + analytic Jacobian blocks of the reprojection rows, one thread per
+ * (camera, frame, joint) observation, compacted to visible observations in residual-row order.
+ *   r2   [n_vis][2]      Jcam [n_vis][2][6] (d/d rvec_c | d/d t_c)     Jpt [n_vis][2][3] (d/d x_p)
+ *   obs_cam, obs_pt [n_vis] int32 (may be NULL): camera / point index of each compacted row pair.
+ * The reference has no Jacobian: SciPy finite-differences ba.objfun (ba.py:187-206). */
+int bax_residual_jacobian(bax_handle* h, const double* theta, double* r2, double* Jcam, double* Jpt,
+                          int32_t* obs_cam, int32_t* obs_pt, void* stream);
+
+/* Jacobian of the two prior families:  Jv3d [n_v3d][3C] (d/d rvecs, includes lambda1);
+ * Jvb [N][B][3] = lambda2 * d r_b / d x[n, bone_b[0]]  (the entry for bone_b[1] is its negative). */
+int bax_prior_jacobian(bax_handle* h, const double* theta, double* Jv3d, double* Jvb, void* stream);
+
+/* ---- trust-region / LM step on the Schur complement (replaces what SciPy's trf_no_bounds does
+ * with the dense FD Jacobian and its SVD: scipy/optimize/_lsq/trf.py:415-587, common.py:57-168).
+ * Every stage is split at the points where a frame-sharded multi-GPU run must sum a small packed
+ * buffer over ranks; bax_reduce_buffer() exposes that buffer (device pointer + length in doubles)
+ * so the host can all-reduce it in place (NCCL via torch.distributed) between the two calls.
+ * On one GPU the *_finish call simply follows. */
+enum { BAX_BUF_BONE = 0, BAX_BUF_COST = 1, BAX_BUF_LIN = 2, BAX_BUF_SCHUR = 3, BAX_BUF_RHS2 = 4,
+       BAX_BUF_STEP = 5 /* not reduced: trial scalars */, BAX_BUF_NORM = 6, BAX_BUF_GMAX = 7 /* MAX-reduced */ };
+int bax_reduce_buffer(bax_handle* h, int which, double** dev_ptr, int64_t* count);
+/* global frame count used by the bone-length variance (sum of N over ranks); default = local N */
+int bax_set_global_frames(bax_handle* h, int64_t n_frames_global);
+
+/* cost = 0.5 * ||objfun(theta)||^2 without materialising the residual vector. */
+int bax_cost_begin(bax_handle* h, const double* theta, void* stream);   /* fills BAX_BUF_BONE  */
+int bax_cost_mid(bax_handle* h, void* stream);                          /* fills BAX_BUF_COST  */
+int bax_cost_finish(bax_handle* h, double* cost_host, void* stream);    /* synchronises        */
+
+/* Linearise at theta: gradient, camera blocks H_cc (reprojection + orientation rows), per-point
+ * 3x3 blocks V_p and g_p.  out_host[0..3] = { cost, ||g||_inf, ||g||_2, ||theta||_2 } */
+int bax_linearize_begin(bax_handle* h, const double* theta, void* stream); /* fills BAX_BUF_BONE */
+int bax_linearize_mid(bax_handle* h, void* stream);                        /* fills BAX_BUF_LIN  */
+int bax_linearize_post(bax_handle* h, void* stream);   /* fills BAX_BUF_NORM (sum) and BAX_BUF_GMAX (max) */
+int bax_linearize_finish(bax_handle* h, double* out_host, void* stream);   /* synchronises       */
+
+/* One damped solve (J^T J + alpha I) p = -g through the per-point Schur complement with the
+ * rank-B Woodbury correction for the bone-length rows; alpha > 0.
+ *   begin : per-point D_p = V_p + alpha I factored in registers, whitened blocks, SYRK  -> BAX_BUF_SCHUR
+ *   mid   : FP64 single-CTA Cholesky of the reduced camera system, back-substitution    -> BAX_BUF_RHS2 / BAX_BUF_STEP
+ *   finish: second reduced solve for phi'(alpha); out_host[0..3] = { ||p||^2, g.p, p^T (H+alpha I)^-1 p, 0 }
+ * step [n] receives p (device). */
+int bax_trial_begin(bax_handle* h, double alpha, void* stream);
+int bax_trial_mid(bax_handle* h, double* step, int need_phi_prime, void* stream);
+int bax_trial_finish(bax_handle* h, double* out_host, void* stream);
+
+/* Weighted linear triangulation of every (frame, joint) — util.triangulate_with_conf,
+ * reference util.py:325-354 (+ triangulate_point 308-322).  R [C][9], t [C][3]; X [N*J][3] (NaN where
+ * the reference returns NaN); status_host: 0 ok, 1 = some point has rank < 3 ("not enough constraint"). */
+int bax_triangulate(bax_handle* h, const double* R, const double* t, double* X, int32_t* status_host,
+                    void* stream);
+
+/* timing hooks for bench.py: CUDA-event time (ms) accumulated on the call's stream per kernel family */
+enum { BAX_T_RJ = 0, BAX_T_BUILD = 1, BAX_T_SYRK = 2, BAX_T_DENSE = 3, BAX_T_BACKSUB = 4, BAX_T_LIN = 5,
+       BAX_T_COST = 6, BAX_T_COUNT = 8 };
+int bax_timing_enable(bax_handle* h, int on);
+int bax_timing_read(bax_handle* h, double* ms_host /*[BAX_T_COUNT]*/, int64_t* launches_host /*[BAX_T_COUNT]*/);
+int bax_timing_reset(bax_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
