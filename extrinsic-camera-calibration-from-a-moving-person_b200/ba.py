@@ -130,7 +130,8 @@ class BAProblem:
         self._views = {}
         if n_frames_global is not None:
             check(self.L.bax_set_global_frames(self.h, int(n_frames_global)), "bax_set_global_frames")
-        self._out4 = (C.c_double * 4)()
+        self._out4 = (C.c_double * 8)()
+        self.h_scale = 0.0
 
     def close(self):
         if getattr(self, "h", None):
@@ -262,7 +263,8 @@ class BAProblem:
                 self._allreduce(_lib.BUF_NORM)
                 self._allreduce(_lib.BUF_GMAX, dist.ReduceOp.MAX)
             check(self.L.bax_linearize_finish(self.h, self._out4, st), "bax_linearize_finish")
-        return tuple(self._out4)
+        self.h_scale = self._out4[4]          # max diagonal of the point blocks of J^T J
+        return tuple(self._out4[:4])
 
     def trial(self, alpha, need_phi_prime=True):
         """Solve (J^T J + alpha I) p = -g; p lands in self.step (device).
@@ -308,21 +310,34 @@ class BAProblem:
 def _solve_tr(prob, Delta, g_norm2, initial_alpha, rtol=0.01, max_iter=10):
     """More'-Sorensen root-finding of ||p(alpha)|| = Delta (scipy/optimize/_lsq/common.py:57-168), with
     every phi / phi' evaluation a damped Schur solve on the GPU instead of an SVD of the dense Jacobian.
-    The exact Jacobian has a 6-dimensional gauge null space, so SciPy's `full_rank` branch (an undamped
-    Gauss-Newton step) never applies and alpha_lower starts at 0."""
+
+    The exact Jacobian has a 6-dimensional gauge null space (plus a nearly flat global-scale mode), so
+    SciPy's `full_rank` branch never applies: alpha_lower starts at 0.  When the minimum-norm Gauss-Newton
+    step lies inside the region (phi < 0 however small alpha gets) SciPy's loop drives alpha to round-off
+    level and follows noise in the null-space singular values; here alpha is floored at
+    1e-13 x the Hessian scale and that interior step is returned unscaled.
+    -> (alpha, iterations, ||p||, g.p, on_boundary)"""
+    alpha_floor = 1e-13 * prob.h_scale
     alpha_upper = g_norm2 / Delta
     alpha_lower = 0.0
+
+    def reset():
+        return max(0.001 * alpha_upper, (alpha_lower * alpha_upper) ** 0.5, alpha_floor)
+
     if initial_alpha is None or initial_alpha == 0:
-        alpha = max(0.001 * alpha_upper, (alpha_lower * alpha_upper) ** 0.5)
+        alpha = reset()
     else:
-        alpha = initial_alpha
+        alpha = max(initial_alpha, alpha_floor)
     it = 0
     for it in range(max_iter):
-        if alpha < alpha_lower or alpha > alpha_upper or not alpha > 0:
-            alpha = max(0.001 * alpha_upper, (alpha_lower * alpha_upper) ** 0.5)
+        if alpha < alpha_lower or alpha > alpha_upper:
+            alpha = reset()
+        alpha = max(alpha, alpha_floor)
         pn2, gp, ptq = prob.trial(alpha, True)
         p_norm = math.sqrt(pn2)
         phi = p_norm - Delta
+        if phi < 0 and alpha <= alpha_floor:
+            return alpha, it + 1, p_norm, gp, False          # interior (Gauss-Newton-like) step
         phi_prime = -ptq / p_norm
         if phi < 0:
             alpha_upper = alpha
@@ -331,10 +346,9 @@ def _solve_tr(prob, Delta, g_norm2, initial_alpha, rtol=0.01, max_iter=10):
         alpha -= (phi + Delta) * ratio / Delta
         if abs(phi) < rtol * Delta:
             break
-    if not alpha > 0:
-        alpha = max(0.001 * alpha_upper, (alpha_lower * alpha_upper) ** 0.5)
+    alpha = max(alpha, alpha_floor)
     pn2, gp, _ = prob.trial(alpha, False)
-    return alpha, it + 1, math.sqrt(pn2), gp
+    return alpha, it + 1, math.sqrt(pn2), gp, True
 
 
 def _update_tr_radius(Delta, actual, predicted, step_norm, bound_hit):
@@ -399,14 +413,14 @@ def trf_schur(prob, theta0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, verb
         actual_reduction = -1.0
         cost_new = cost
         while actual_reduction <= 0 and nfev < max_nfev:
-            alpha, n_it, p_norm, gdotp = _solve_tr(prob, Delta, g_2, alpha)
-            kappa = Delta / p_norm                   # SciPy rescales the step onto the boundary
+            alpha, n_it, p_norm, gdotp, on_boundary = _solve_tr(prob, Delta, g_2, alpha)
+            kappa = Delta / p_norm if on_boundary else 1.0   # SciPy rescales a boundary step onto the boundary
             # -(0.5 ||J s||^2 + g.s) with s = kappa p and p^T J^T J p = -g.p - alpha ||p||^2
             predicted = -(0.5 * kappa * kappa * (-gdotp - alpha * p_norm * p_norm) + kappa * gdotp)
             torch.add(x, prob.step, alpha=kappa, out=x_new)
             cost_new = prob.cost(x_new)
             nfev += 1
-            step_norm = Delta
+            step_norm = kappa * p_norm
             if not math.isfinite(cost_new):
                 Delta = 0.25 * step_norm
                 continue

@@ -260,10 +260,11 @@ __device__ __forceinline__ void bone_u(const double* __restrict__ x, int64_t fra
 __global__ void __launch_bounds__(256)
 k_gp_bone(const double* __restrict__ x, int64_t P, int J, const int32_t* __restrict__ bones,
           const int32_t* __restrict__ joint_bones, const double* __restrict__ Lbar, const double* __restrict__ rb,
-          double scale, double* __restrict__ gp, double* __restrict__ part /*[grid][2]*/, double* __restrict__ pmax) {
+          double scale, double* __restrict__ gp, const double* __restrict__ Vp,
+          double* __restrict__ part /*[grid][2]*/, double* __restrict__ pmax /*[2][grid]*/) {
   __shared__ double sm[2 * 32];
-  __shared__ double smax[8];
-  double acc[2] = {0, 0}, mx = 0;
+  __shared__ double smax[16];
+  double acc[2] = {0, 0}, mx = 0, mv = 0;
   for (int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x; p < P; p += (int64_t)gridDim.x * 256) {
     int j = (int)(p % J); int64_t fb = (p - j) * 3;
     double g0 = gp[3 * p], g1 = gp[3 * p + 1], g2 = gp[3 * p + 2];
@@ -281,14 +282,18 @@ k_gp_bone(const double* __restrict__ x, int64_t P, int J, const int32_t* __restr
     acc[0] += g0 * g0 + g1 * g1 + g2 * g2;
     acc[1] += x[3 * p] * x[3 * p] + x[3 * p + 1] * x[3 * p + 1] + x[3 * p + 2] * x[3 * p + 2];
     mx = fmax(mx, fmax(fabs(g0), fmax(fabs(g1), fabs(g2))));
+    mv = fmax(mv, fmax(Vp[6 * p], fmax(Vp[6 * p + 3], Vp[6 * p + 5])));
   }
-  for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-  if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = mx;
+  for (int o = 16; o > 0; o >>= 1) {
+    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    mv = fmax(mv, __shfl_xor_sync(0xffffffffu, mv, o));
+  }
+  if ((threadIdx.x & 31) == 0) { smax[threadIdx.x >> 5] = mx; smax[8 + (threadIdx.x >> 5)] = mv; }
   block_sum<2>(acc, sm);
   if (threadIdx.x == 0) {
-    for (int w = 0; w < 8; ++w) mx = fmax(mx, smax[w]);
+    for (int w = 0; w < 8; ++w) { mx = fmax(mx, smax[w]); mv = fmax(mv, smax[8 + w]); }
     part[2 * blockIdx.x] = acc[0]; part[2 * blockIdx.x + 1] = acc[1];
-    pmax[blockIdx.x] = mx;
+    pmax[blockIdx.x] = mx; pmax[gridDim.x + blockIdx.x] = mv;
   }
 }
 __global__ void k_reduce_max(const double* __restrict__ v, int n, double* __restrict__ out) {
@@ -373,10 +378,11 @@ extern "C" int bax_linearize_post(bax_handle* h, void* stream) {
   // scale = lam2 * 2 / Ntot ; Ntot lives on device (buf[BONE][B]); single-GPU fast path reads host N,
   // multi-GPU callers set it through bax_set_global_frames before linearising.
   double scale = h->lam2 * 2.0 / (double)h->n_frames_global;
-  k_gp_bone<<<g, 256, 0, s>>>(h->theta_lin + C6, h->P, h->J, h->bones, h->joint_bones, h->Lbar, h->rb, scale, h->gp, part, pmax);
+  k_gp_bone<<<g, 256, 0, s>>>(h->theta_lin + C6, h->P, h->J, h->bones, h->joint_bones, h->Lbar, h->rb, scale, h->gp, h->Vp, part, pmax);
   BAX_LAUNCH_CHECK();
   int rc = bax_reduce_partials(h, part, g, 2, h->buf[BAX_BUF_NORM], s); if (rc) return rc;
   k_reduce_max<<<1, 256, 0, s>>>(pmax, g, h->buf[BAX_BUF_GMAX]);
+  k_reduce_max<<<1, 256, 0, s>>>(pmax + g, g, h->buf[BAX_BUF_GMAX] + 1);
   BAX_LAUNCH_CHECK();
   return BAX_OK;
 }
@@ -390,6 +396,7 @@ extern "C" int bax_linearize_finish(bax_handle* h, double* out_host, void* strea
   BAX_CUDA(cudaMemcpyAsync(stage, lin + (size_t)C6 * C6, sizeof(double) * (C6 + B + 2), cudaMemcpyDeviceToHost, s));
   BAX_CUDA(cudaMemcpyAsync(stage + C6 + B + 2, h->buf[BAX_BUF_NORM], sizeof(double) * 2, cudaMemcpyDeviceToHost, s));
   BAX_CUDA(cudaMemcpyAsync(stage + C6 + B + 4, h->buf[BAX_BUF_GMAX], sizeof(double), cudaMemcpyDeviceToHost, s));
+  BAX_CUDA(cudaMemcpyAsync(stage + C6 + B + 6, h->buf[BAX_BUF_GMAX] + 1, sizeof(double), cudaMemcpyDeviceToHost, s));
   BAX_CUDA(cudaMemcpyAsync(stage + C6 + B + 5, h->buf[BAX_BUF_BONE] + B, sizeof(double), cudaMemcpyDeviceToHost, s));
   BAX_CUDA(cudaMemcpyAsync(stage + C6 + B + 8, h->theta_lin, sizeof(double) * C6, cudaMemcpyDeviceToHost, s));
   BAX_CUDA(cudaStreamSynchronize(s));
@@ -398,6 +405,7 @@ extern "C" int bax_linearize_finish(bax_handle* h, double* out_host, void* strea
   for (int i = 0; i < C6; ++i) { ginf = fmax(ginf, fabs(gc[i])); g2 += gc[i] * gc[i]; x2 += stage[C6 + B + 8 + i] * stage[C6 + B + 8 + i]; }
   h->cost = 0.5 * (stage[C6 + B] + stage[C6 + B + 1] + bone_cost_host(h, ssq, stage[C6 + B + 5]));
   out_host[0] = h->cost; out_host[1] = ginf; out_host[2] = sqrt(g2); out_host[3] = sqrt(x2);
+  out_host[4] = stage[C6 + B + 6];
   return BAX_OK;
 }
 

@@ -279,7 +279,7 @@ extern "C" int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B
   h->buf_count[BAX_BUF_RHS2] = C6 + B + 4;
   h->buf_count[BAX_BUF_STEP] = 4;
   h->buf_count[BAX_BUF_NORM] = 4;
-  h->buf_count[BAX_BUF_GMAX] = 1;
+  h->buf_count[BAX_BUF_GMAX] = 2;
   for (int i = 0; i < 8; ++i) {
     BAX_CUDA(cudaMalloc(&h->buf[i], sizeof(double) * (h->buf_count[i] > 0 ? h->buf_count[i] : 1)));
     BAX_CUDA(cudaMemsetAsync(h->buf[i], 0, sizeof(double) * (h->buf_count[i] > 0 ? h->buf_count[i] : 1), s));

@@ -116,7 +116,7 @@ __global__ void k_var3d_residual(const double* __restrict__ campack, const doubl
 __global__ void __launch_bounds__(256)
 k_bone_len(const double* __restrict__ x, int N, int J, int B, const int32_t* __restrict__ bones,
            const double* __restrict__ bone_buf /* null in pass 1: [B] sums, [B] = count */,
-           double* __restrict__ part /*[gridDim.x][BAX_MAX_B]*/) {
+           double* __restrict__ part /*[gridDim.x][B]*/) {
   __shared__ double sm[BAX_MAX_B * 32];
   double acc[BAX_MAX_B];
 #pragma unroll
@@ -137,7 +137,7 @@ k_bone_len(const double* __restrict__ x, int N, int J, int B, const int32_t* __r
   }
   block_sum<BAX_MAX_B>(acc, sm);
   if (threadIdx.x == 0)
-    for (int b = 0; b < BAX_MAX_B; ++b) part[(size_t)blockIdx.x * BAX_MAX_B + b] = acc[b];
+    for (int b = 0; b < B; ++b) part[(size_t)blockIdx.x * B + b] = acc[b];
 }
 __global__ void k_set_scalar(double* p, double v) { *p = v; }
 __global__ void k_bone_rows(const double* __restrict__ ssq, const double* __restrict__ bone_buf, int B,

@@ -78,7 +78,7 @@ int bax_cost_mid(bax_handle* h, void* stream);                          /* fills
 int bax_cost_finish(bax_handle* h, double* cost_host, void* stream);    /* synchronises        */
 
 /* Linearise at theta: gradient, camera blocks H_cc (reprojection + orientation rows), per-point
- * 3x3 blocks V_p and g_p.  out_host[0..3] = { cost, ||g||_inf, ||g||_2, ||theta||_2 } */
+ * 3x3 blocks V_p and g_p.  out_host[0..4] = { cost, ||g||_inf, ||g||_2, ||theta||_2, max diag V_p } */
 int bax_linearize_begin(bax_handle* h, const double* theta, void* stream); /* fills BAX_BUF_BONE */
 int bax_linearize_mid(bax_handle* h, void* stream);                        /* fills BAX_BUF_LIN  */
 int bax_linearize_post(bax_handle* h, void* stream);   /* fills BAX_BUF_NORM (sum) and BAX_BUF_GMAX (max) */

