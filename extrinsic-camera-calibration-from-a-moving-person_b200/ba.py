@@ -386,69 +386,92 @@ TERMINATION_MESSAGES = {0: "The maximum number of function evaluations is exceed
                         4: "Both `ftol` and `xtol` termination conditions are satisfied."}
 
 
-def trf_schur(prob, theta0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, verbose=0, callback=None):
+class TRFSolver:
     """Trust-region-reflective loop of SciPy's `trf_no_bounds` (scipy/optimize/_lsq/trf.py:415-587,
     x_scale = 1, tr_solver = 'exact') — the solver reference ba.py:187-206 runs — with the Jacobian,
-    normal equations and damped solves on the GPU.  Returns a dict like OptimizeResult."""
-    x = prob._dev_theta(theta0).clone()
-    cost, g_inf, g_2, x_norm = prob.linearize(x)
-    if not math.isfinite(cost):
-        raise ValueError("Residuals are not finite in the initial point.")
-    initial_cost = cost
-    nfev, njev = 1, 1
-    n = prob.n
-    if max_nfev is None:
-        max_nfev = 100 * n
-    Delta = x_norm if x_norm > 0 else 1.0
-    alpha = 0.0
-    status = None
-    iteration = 0
-    history = []
-    x_new = torch.empty_like(x)
-    while True:
-        if g_inf < gtol:
-            status = 1
-        if status is not None or nfev == max_nfev:
-            break
+    normal equations and damped solves on the GPU.  `iterate()` is one pass of SciPy's outer loop body:
+    trust-region solves and cost evaluations until a step is accepted (or evaluations run out), then a
+    re-linearisation."""
+
+    def __init__(self, prob, theta0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None):
+        self.prob = prob
+        self.x = prob._dev_theta(theta0).clone()
+        self.x_new = torch.empty_like(self.x)
+        self.ftol, self.xtol, self.gtol = ftol, xtol, gtol
+        self.cost, self.g_inf, self.g_2, self.x_norm = prob.linearize(self.x)
+        if not math.isfinite(self.cost):
+            raise ValueError("Residuals are not finite in the initial point.")
+        self.initial_cost = self.cost
+        self.nfev, self.njev = 1, 1
+        self.max_nfev = 100 * prob.n if max_nfev is None else max_nfev
+        self.Delta = self.x_norm if self.x_norm > 0 else 1.0
+        self.alpha = 0.0
+        self.status = None
+        self.iteration = 0
+        self.history = []
+
+    def done(self):
+        if self.status is None and self.g_inf < self.gtol:
+            self.status = 1
+        return self.status is not None or self.nfev >= self.max_nfev
+
+    def iterate(self, relinearize=True):
+        prob = self.prob
         actual_reduction = -1.0
-        cost_new = cost
-        while actual_reduction <= 0 and nfev < max_nfev:
-            alpha, n_it, p_norm, gdotp, on_boundary = _solve_tr(prob, Delta, g_2, alpha)
-            kappa = Delta / p_norm if on_boundary else 1.0   # SciPy rescales a boundary step onto the boundary
+        cost_new = self.cost
+        while actual_reduction <= 0 and self.nfev < self.max_nfev:
+            self.alpha, n_it, p_norm, gdotp, on_boundary = _solve_tr(prob, self.Delta, self.g_2, self.alpha)
+            alpha = self.alpha
+            kappa = self.Delta / p_norm if on_boundary else 1.0   # SciPy rescales a boundary step onto the boundary
             # -(0.5 ||J s||^2 + g.s) with s = kappa p and p^T J^T J p = -g.p - alpha ||p||^2
             predicted = -(0.5 * kappa * kappa * (-gdotp - alpha * p_norm * p_norm) + kappa * gdotp)
-            torch.add(x, prob.step, alpha=kappa, out=x_new)
-            cost_new = prob.cost(x_new)
-            nfev += 1
+            torch.add(self.x, prob.step, alpha=kappa, out=self.x_new)
+            cost_new = prob.cost(self.x_new)
+            self.nfev += 1
             step_norm = kappa * p_norm
             if not math.isfinite(cost_new):
-                Delta = 0.25 * step_norm
+                self.Delta = 0.25 * step_norm
                 continue
-            actual_reduction = cost - cost_new
-            Delta_new, ratio = _update_tr_radius(Delta, actual_reduction, predicted, step_norm,
-                                                 step_norm > 0.95 * Delta)
-            history.append(dict(alpha=alpha, Delta=Delta, step_norm=step_norm, cost_new=cost_new,
-                                pred=predicted, act=actual_reduction, n_it=n_it))
-            status = _check_termination(actual_reduction, cost, step_norm, x_norm, ratio, ftol, xtol)
-            if status is not None:
+            actual_reduction = self.cost - cost_new
+            Delta_new, ratio = _update_tr_radius(self.Delta, actual_reduction, predicted, step_norm,
+                                                 step_norm > 0.95 * self.Delta)
+            self.history.append(dict(alpha=alpha, Delta=self.Delta, step_norm=step_norm, cost_new=cost_new,
+                                     pred=predicted, act=actual_reduction, n_it=n_it))
+            self.status = _check_termination(actual_reduction, self.cost, step_norm, self.x_norm, ratio,
+                                             self.ftol, self.xtol)
+            if self.status is not None:
                 break
-            alpha *= Delta / Delta_new
-            Delta = Delta_new
+            self.alpha *= self.Delta / Delta_new
+            self.Delta = Delta_new
         if actual_reduction > 0:
-            x, x_new = x_new, x
-            cost, g_inf, g_2, x_norm = prob.linearize(x)
-            njev += 1
-        iteration += 1
+            self.x, self.x_new = self.x_new, self.x
+            if relinearize:
+                self.cost, self.g_inf, self.g_2, self.x_norm = prob.linearize(self.x)
+                self.njev += 1
+            else:
+                self.cost = cost_new
+        self.iteration += 1
+
+    def result(self):
+        status = 0 if self.status is None else self.status
+        return dict(x=self.x, cost=self.cost, optimality=self.g_inf, nfev=self.nfev, njev=self.njev,
+                    status=status, iterations=self.iteration, history=self.history,
+                    message=TERMINATION_MESSAGES[status], initial_cost=self.initial_cost)
+
+
+def trf_schur(prob, theta0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, verbose=0, callback=None):
+    """Run TRFSolver to termination.  Returns a dict like SciPy's OptimizeResult (x stays on the device)."""
+    sol = TRFSolver(prob, theta0, ftol, xtol, gtol, max_nfev)
+    while not sol.done():
+        sol.iterate()
         if callback is not None:
-            callback(iteration, cost, nfev)
-    if status is None:
-        status = 0
+            callback(sol.iteration, sol.cost, sol.nfev)
+    res = sol.result()
     if verbose:
-        print(TERMINATION_MESSAGES[status])
-        print(f"Function evaluations {nfev}, initial cost {initial_cost:.4e}, final cost {cost:.4e}, "
-              f"first-order optimality {g_inf:.2e}.")
-    return dict(x=x, cost=cost, optimality=g_inf, nfev=nfev, njev=njev, status=status,
-                iterations=iteration, history=history, message=TERMINATION_MESSAGES[status])
+        print(res["message"])
+        print(f"Function evaluations {res['nfev']}, initial cost {res['initial_cost']:.4e}, "
+              f"final cost {res['cost']:.4e}, first-order optimality {res['optimality']:.2e}.")
+    return res
 
 
 # ----------------------------------------------------------------------------- reference entry points
