@@ -300,13 +300,11 @@ def run_gpu(args):
                 "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
                 "clocks": sampler.summary()}
     # ---------------- RANSAC leg (hypotheses/s), BASELINE configs[1]
-    try:
-        from calib_b200 import calib_ransac as cr
-        rs = cr.bench_leg(rank, world, dev, steps=max(1, min(args.steps, 3)), no_cpu=args.no_cpu or world > 1)
-        if line is not None:
-            line["ransac"] = rs
-    except ImportError:
-        pass
+    from calib_b200 import calib_ransac as cr
+    rs = cr.bench_leg(rank, world, dev, steps=max(1, min(args.steps, 3)), no_cpu=args.no_cpu or world > 1)
+    if line is not None:
+        line["ransac"] = rs
+        line["gpu_launches"] = int(launches) + sum(v["launches"] for v in rs["kernel_ms_one_pass"].values()) * max(1, min(args.steps, 3))
     if rank == 0:
         print(json.dumps(line))
     prob.close()

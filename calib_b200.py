@@ -1,10 +1,18 @@
-"""Importable alias of the package directory (whose contract-mandated name contains hyphens)."""
+"""Importable alias of the package directory (whose contract-mandated name contains hyphens).
+
+`import calib_b200` binds the package and every submodule under both names to ONE module object each, so
+`calib_b200.ba` and `extrinsic-camera-calibration-from-a-moving-person_b200.ba` can never diverge."""
 import importlib
 import os
 import sys
 
+_NAME = "extrinsic-camera-calibration-from-a-moving-person_b200"
 _here = os.path.dirname(os.path.abspath(__file__))
 if _here not in sys.path:
     sys.path.insert(0, _here)
-_pkg = importlib.import_module("extrinsic-camera-calibration-from-a-moving-person_b200")
-sys.modules[__name__] = _pkg
+_pkg = importlib.import_module(_NAME)
+for _sub in ("_lib", "_rsx_sigs", "scene", "ba", "calib_ransac", "dataio", "cli"):
+    if os.path.isfile(os.path.join(_here, _NAME, _sub + ".py")):
+        _m = importlib.import_module(_NAME + "." + _sub)
+        sys.modules["calib_b200." + _sub] = _m
+sys.modules["calib_b200"] = _pkg

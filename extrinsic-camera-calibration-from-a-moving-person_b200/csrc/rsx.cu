@@ -1,0 +1,311 @@
+// RANSAC linear calibration on the GPU: one CTA fits one minimal-sample hypothesis, one CTA scores one model
+// against every ray and bone direction (reference calib_ransac.py:134-209).
+#include "rsx_handle.cuh"
+#include "rsx_fit.cuh"
+#include <stdlib.h>
+#include <string.h>
+
+#define FIT_THREADS 128
+#define SCORE_THREADS 256
+
+// ------------------------------------------------------------------ kernels
+__global__ void __launch_bounds__(FIT_THREADS)
+k_rsx_fit(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
+          const int32_t* __restrict__ samp_v, const int32_t* __restrict__ samp_m, int64_t H,
+          double* __restrict__ Rt, double* __restrict__ hv_global /*null: H, V in shared memory*/) {
+  extern __shared__ __align__(16) double sm[];
+  const int nu = 3 * (RSX_S + C), ld = nu | 1;
+  FitWs ws;
+  fit_ws_carve(sm, hv_global ? hv_global + (size_t)blockIdx.x * 2 * nu * ld : nullptr, C, ws);
+  CtaCtx g{(int)threadIdx.x, (int)blockDim.x};
+  for (int64_t h = blockIdx.x; h < H; h += gridDim.x)
+    fit_hypothesis(g, C, N, M, v, n, samp_v + h * RSX_S, samp_m + h * RSX_S, ws, Rt + (size_t)h * C * 12);
+}
+
+__global__ void __launch_bounds__(SCORE_THREADS)
+k_rsx_score(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
+            const double* __restrict__ Rt, int64_t H, double* __restrict__ score, double* __restrict__ parts) {
+  extern __shared__ __align__(16) double sm[];       // [C][12] model, then 2*32 reduction scratch
+  double* sRt = sm;
+  double* red = sm + ((12 * C + 1) & ~1);
+  CtaCtx g{(int)threadIdx.x, (int)blockDim.x};
+  for (int64_t h = blockIdx.x; h < H; h += gridDim.x) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < 12 * C; i += blockDim.x) sRt[i] = Rt[(size_t)h * C * 12 + i];
+    __syncthreads();
+    double acc[2];
+    acc[0] = score_points(g, C, M, n, sRt, nullptr, nullptr, 0.0, nullptr);
+    acc[1] = score_dirs(g, C, N, v, sRt, nullptr, 0.0, nullptr);
+    block_sum<2>(acc, red);
+    if (threadIdx.x == 0) {
+      score[h] = sqrt(acc[0]) / (double)M + sqrt(acc[1]) / (double)N;      // calib_ransac.py:179-181
+      if (parts) { parts[2 * h] = acc[0]; parts[2 * h + 1] = acc[1]; }
+    }
+  }
+}
+
+// first minimum under strict '<' starting from +inf (calib_ransac.py:139,182): NaN / +inf never win
+__global__ void __launch_bounds__(1024)
+k_rsx_argmin(const double* __restrict__ score, int64_t H, double* __restrict__ out /*[2]: index, score*/) {
+  __shared__ double sv[32]; __shared__ long long si[32];
+  double bv = INFINITY; long long bi = -1;
+  for (int64_t i = threadIdx.x; i < H; i += blockDim.x) {
+    const double s = score[i];
+    if (s < bv) { bv = s; bi = i; }                 // strided scan keeps the lowest index per thread
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
+    const long long oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (oi >= 0 && (ov < bv || (ov == bv && (bi < 0 || oi < bi)))) { bv = ov; bi = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = bv; si[threadIdx.x >> 5] = bi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w)
+      if (si[w] >= 0 && (sv[w] < bv || (sv[w] == bv && (bi < 0 || si[w] < bi)))) { bv = sv[w]; bi = si[w]; }
+    out[0] = (double)bi; out[1] = bv;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_rsx_masks(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
+            const double* __restrict__ Rt, const double* __restrict__ K00, double th2d, double th3d,
+            uint8_t* __restrict__ mask2d, uint8_t* __restrict__ mask3d, double* __restrict__ e_out,
+            double* __restrict__ e3d_out) {
+  extern __shared__ __align__(16) double sm[];       // [C][12] model, [C] focal lengths
+  for (int i = threadIdx.x; i < 12 * C; i += blockDim.x) sm[i] = Rt[i];
+  for (int i = threadIdx.x; i < C; i += blockDim.x) sm[12 * C + i] = K00[i];
+  __syncthreads();
+  CtaCtx g{(int)(blockIdx.x * blockDim.x + threadIdx.x), (int)(gridDim.x * blockDim.x)};
+  score_points(g, C, M, n, sm, e_out, sm + 12 * C, th2d, mask2d);
+  score_dirs(g, C, N, v, sm, e3d_out, th3d, mask3d);
+}
+
+__global__ void k_rsx_count(const uint8_t* __restrict__ m, int64_t n, unsigned long long* __restrict__ out) {
+  unsigned long long c = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) c += m[i];
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
+}
+
+// ------------------------------------------------------------------ handle
+extern "C" int rsx_create(int device, rsx_handle** out) {
+  if (!out) { bax_set_error("rsx_create: null out"); return BAX_E_ARG; }
+  BAX_CUDA(cudaSetDevice(device));
+  rsx_handle* h = (rsx_handle*)calloc(1, sizeof(rsx_handle));
+  h->device = device;
+  cudaDeviceProp prop;
+  BAX_CUDA(cudaGetDeviceProperties(&prop, device));
+  h->sm_count = prop.multiProcessorCount;
+  BAX_CUDA(cudaEventCreate(&h->ev0));
+  BAX_CUDA(cudaEventCreate(&h->ev1));
+  BAX_CUDA(cudaMallocHost((void**)&h->host_pinned, 64 * sizeof(double)));
+  h->red_bytes = sizeof(double) * (1 << 20);
+  BAX_CUDA(cudaMalloc(&h->red, h->red_bytes));
+  h->bx = (bax_handle*)calloc(1, sizeof(bax_handle));
+  h->bx->device = device; h->bx->sm_count = h->sm_count;
+  *out = h;
+  return BAX_OK;
+}
+
+static void rsx_free_problem(rsx_handle* h) {
+  void* ptrs[] = {h->v, h->n, h->Rt, h->fit_scratch};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  h->v = h->n = h->Rt = h->fit_scratch = nullptr; h->cap_h = 0; h->fit_scratch_bytes = 0;
+}
+
+extern "C" int rsx_destroy(rsx_handle* h) {
+  if (!h) return BAX_OK;
+  cudaSetDevice(h->device);
+  rsx_free_problem(h);
+  if (h->bx) { if (h->bx->syrk_part) cudaFree(h->bx->syrk_part); if (h->bx->partials) cudaFree(h->bx->partials); free(h->bx); }
+  cudaFree(h->red); cudaFreeHost(h->host_pinned);
+  cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
+  free(h);
+  return BAX_OK;
+}
+
+extern "C" int rsx_problem_set(rsx_handle* h, int C, int64_t N, int64_t M, const double* v, const double* n, void* stream) {
+  if (!h || C < 2 || N < RSX_S || M < RSX_S || !v || !n) {
+    bax_set_error("rsx_problem_set: needs C >= 2 cameras and at least %d directions and rays", RSX_S); return BAX_E_ARG;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  BAX_CUDA(cudaSetDevice(h->device));
+  rsx_free_problem(h);
+  h->C = C; h->N = N; h->M = M;
+  BAX_CUDA(cudaMalloc(&h->v, sizeof(double) * 3 * C * N));
+  BAX_CUDA(cudaMalloc(&h->n, sizeof(double) * 3 * C * M));
+  BAX_CUDA(cudaMemcpyAsync(h->v, v, sizeof(double) * 3 * C * N, cudaMemcpyDeviceToDevice, s));
+  BAX_CUDA(cudaMemcpyAsync(h->n, n, sizeof(double) * 3 * C * M, cudaMemcpyDeviceToDevice, s));
+  BAX_CUDA(cudaStreamSynchronize(s));
+  return BAX_OK;
+}
+
+static int ensure_models(rsx_handle* h, int64_t H) {
+  if (H > h->cap_h) {
+    if (h->Rt) cudaFree(h->Rt);
+    h->Rt = nullptr; h->cap_h = 0;
+    BAX_CUDA(cudaMalloc(&h->Rt, sizeof(double) * 12 * h->C * H));
+    h->cap_h = H;
+  }
+  return BAX_OK;
+}
+
+int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, int64_t H, double* Rt, cudaStream_t s) {
+  const int C = h->C, nu = 3 * (RSX_S + C), ld = nu | 1;
+  const size_t small = fit_ws_small_doubles(C) * sizeof(double);
+  const size_t hv = sizeof(double) * 2 * (size_t)nu * ld;
+  int64_t grid = H;
+  double* hvg = nullptr;
+  size_t smem = small + hv;
+  if (smem > 200 * 1024) {                       // many cameras: eigen-solver workspace in global memory (L2)
+    smem = small;
+    grid = H < 2 * h->sm_count ? H : 2 * h->sm_count;
+    if (hv * grid > h->fit_scratch_bytes) {
+      if (h->fit_scratch) cudaFree(h->fit_scratch);
+      h->fit_scratch = nullptr; h->fit_scratch_bytes = 0;
+      BAX_CUDA(cudaMalloc(&h->fit_scratch, hv * grid));
+      h->fit_scratch_bytes = hv * grid;
+    }
+    hvg = h->fit_scratch;
+  } else if (grid > 64 * (int64_t)h->sm_count) {
+    grid = 64 * (int64_t)h->sm_count;
+  }
+  BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  RsxTimer t(h, RSX_T_FIT, s, 1);
+  k_rsx_fit<<<(unsigned)grid, FIT_THREADS, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt, hvg);
+  BAX_LAUNCH_CHECK();
+  return BAX_OK;
+}
+
+extern "C" int rsx_fit_score(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, int64_t H, double* score,
+                             double* Rt, double* parts, void* stream) {
+  if (!h || !h->v || !samp_v || !samp_m || H < 1 || !score) { bax_set_error("rsx_fit_score: bad argument / no problem"); return BAX_E_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  BAX_CUDA(cudaSetDevice(h->device));
+  double* models = Rt;
+  if (!models) { int rc = ensure_models(h, H); if (rc) return rc; models = h->Rt; }
+  int rc = rsx_launch_fit(h, samp_v, samp_m, H, models, s); if (rc) return rc;
+  {
+    const size_t smem = sizeof(double) * (((12 * h->C + 1) & ~1) + 2 * 32);
+    int64_t grid = H < 64 * (int64_t)h->sm_count ? H : 64 * (int64_t)h->sm_count;
+    RsxTimer t(h, RSX_T_SCORE, s, 1);
+    k_rsx_score<<<(unsigned)grid, SCORE_THREADS, smem, s>>>(h->C, h->N, h->M, h->v, h->n, models, H, score, parts);
+    BAX_LAUNCH_CHECK();
+  }
+  return BAX_OK;
+}
+
+extern "C" int rsx_argmin(rsx_handle* h, const double* score, int64_t H, int64_t* best_host, double* score_host, void* stream) {
+  if (!h || !score || H < 1 || !best_host) { bax_set_error("rsx_argmin: bad argument"); return BAX_E_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  BAX_CUDA(cudaSetDevice(h->device));
+  {
+    RsxTimer t(h, RSX_T_OTHER, s, 1);
+    k_rsx_argmin<<<1, 1024, 0, s>>>(score, H, h->red);
+    BAX_LAUNCH_CHECK();
+  }
+  BAX_CUDA(cudaMemcpyAsync(h->host_pinned, h->red, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  BAX_CUDA(cudaStreamSynchronize(s));
+  best_host[0] = (int64_t)h->host_pinned[0];
+  if (score_host) score_host[0] = h->host_pinned[1];
+  return BAX_OK;
+}
+
+extern "C" int rsx_winner_masks(rsx_handle* h, const double* Rt, const double* K00, double th2d, double th3d,
+                                uint8_t* mask2d, uint8_t* mask3d, double* e_out, double* e3d_out,
+                                int64_t* counts_host, void* stream) {
+  if (!h || !h->v || !Rt || !K00 || !mask2d || !mask3d) { bax_set_error("rsx_winner_masks: bad argument / no problem"); return BAX_E_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  BAX_CUDA(cudaSetDevice(h->device));
+  const int64_t mx = h->M > h->N ? h->M : h->N;
+  int grid = (int)((mx + 255) / 256); if (grid > 8 * h->sm_count) grid = 8 * h->sm_count;
+  unsigned long long* cnt = (unsigned long long*)h->red;
+  BAX_CUDA(cudaMemsetAsync(cnt, 0, 2 * sizeof(unsigned long long), s));
+  {
+    RsxTimer t(h, RSX_T_OTHER, s, 3);
+    k_rsx_masks<<<grid, 256, sizeof(double) * 13 * h->C, s>>>(h->C, h->N, h->M, h->v, h->n, Rt, K00, th2d, th3d,
+                                                             mask2d, mask3d, e_out, e3d_out);
+    BAX_LAUNCH_CHECK();
+    k_rsx_count<<<64, 256, 0, s>>>(mask2d, h->M, cnt);
+    k_rsx_count<<<64, 256, 0, s>>>(mask3d, h->N, cnt + 1);
+    BAX_LAUNCH_CHECK();
+  }
+  unsigned long long hc[2] = {0, 0};
+  BAX_CUDA(cudaMemcpyAsync(hc, cnt, sizeof(hc), cudaMemcpyDeviceToHost, s));
+  BAX_CUDA(cudaStreamSynchronize(s));
+  if (counts_host) { counts_host[0] = (int64_t)hc[0]; counts_host[1] = (int64_t)hc[1]; }
+  return BAX_OK;
+}
+
+extern "C" int rsx_timing_enable(rsx_handle* h, int on) {
+  h->timing = on;
+  for (int i = 0; i < RSX_T_COUNT; ++i) { h->t_ms[i] = 0; h->t_launch[i] = 0; }
+  return BAX_OK;
+}
+extern "C" int rsx_timing_read(rsx_handle* h, double* ms, int64_t* nl) {
+  for (int i = 0; i < RSX_T_COUNT; ++i) { if (ms) ms[i] = h->t_ms[i]; if (nl) nl[i] = h->t_launch[i]; }
+  return BAX_OK;
+}
+
+// ------------------------------------------------------------------ host: NumPy-compatible sample stream
+// PCG64 = pcg_setseq_128_xsl_rr_64 (NumPy's default BitGenerator), 32-bit draws served low half first.
+namespace {
+typedef unsigned __int128 u128;
+struct Pcg64 {
+  u128 state, inc; int has32; uint32_t buf;
+  inline uint64_t next64() {
+    const u128 mult = ((u128)2549297995355413924ULL << 64) | (u128)4865540595714422341ULL;
+    state = state * mult + inc;
+    const uint64_t hi = (uint64_t)(state >> 64), lo = (uint64_t)state, x = hi ^ lo;
+    const unsigned r = (unsigned)(state >> 122);
+    return (x >> r) | (x << ((64 - r) & 63));
+  }
+  inline uint32_t next32() {
+    if (has32) { has32 = 0; return buf; }
+    const uint64_t v = next64();
+    has32 = 1; buf = (uint32_t)(v >> 32);
+    return (uint32_t)v;
+  }
+  // random_bounded_uint64(off = 0, rng, mask = 0, use_masked = false) for rng < 2^32 - 1: Lemire's method
+  inline uint32_t bounded(uint32_t rng) {
+    if (rng == 0) return 0;
+    const uint32_t rng_excl = rng + 1;
+    uint64_t m = (uint64_t)next32() * rng_excl;
+    uint32_t left = (uint32_t)m;
+    if (left < rng_excl) {
+      const uint32_t th = (0xffffffffu - rng) % rng_excl;
+      while (left < th) { m = (uint64_t)next32() * rng_excl; left = (uint32_t)m; }
+    }
+    return (uint32_t)(m >> 32);
+  }
+  // Generator.choice(pop, size = 10, replace = False): Floyd's sampling, then _shuffle_int
+  inline void choice10(int64_t pop, int32_t* out) {
+    for (int k = 0; k < RSX_SAMPLE; ++k) {
+      const int64_t j = pop - RSX_SAMPLE + k;
+      int64_t val = bounded((uint32_t)j);
+      for (int q = 0; q < k; ++q) if (out[q] == val) { val = j; break; }
+      out[k] = (int32_t)val;
+    }
+    for (int i = RSX_SAMPLE - 1; i >= 1; --i) {
+      const uint32_t j = bounded((uint32_t)i);
+      const int32_t tmp = out[i]; out[i] = out[j]; out[j] = tmp;
+    }
+  }
+};
+}  // namespace
+
+extern "C" int rsx_sample_stream(uint64_t* pcg, int64_t N, int64_t M, int64_t H, int32_t* samp_v, int32_t* samp_m) {
+  if (!pcg || !samp_v || !samp_m || N < RSX_SAMPLE || M < RSX_SAMPLE || H < 0 || N >= 0x7fffffffLL || M >= 0x7fffffffLL) {
+    bax_set_error("rsx_sample_stream: bad argument (populations must hold %d..2^31-2 items)", RSX_SAMPLE); return BAX_E_ARG;
+  }
+  Pcg64 g;
+  g.state = ((u128)pcg[0] << 64) | pcg[1]; g.inc = ((u128)pcg[2] << 64) | pcg[3];
+  g.has32 = (int)pcg[4]; g.buf = (uint32_t)pcg[5];
+  for (int64_t h = 0; h < H; ++h) {
+    g.choice10(N, samp_v + h * RSX_SAMPLE);
+    g.choice10(M, samp_m + h * RSX_SAMPLE);
+  }
+  pcg[0] = (uint64_t)(g.state >> 64); pcg[1] = (uint64_t)g.state; pcg[4] = (uint64_t)g.has32; pcg[5] = g.buf;
+  return BAX_OK;
+}

@@ -1,0 +1,633 @@
+// calib_linear on large (inlier) sets — reference calib_ransac.py:51-131 as called at :209 — without
+// densifying the 3(M+C) x 3(M+C) normal matrix.
+//
+// Unknowns u = [X_0..X_{M-1} | t_0..t_{C-1}].  H = A^T A is an arrow matrix:
+//   H[X_i,X_i] = D_i = sum_c Q_ci^T Q_ci (3x3),  Q_ci = hat(n_ci) R_c          collinearity rows, :24-33
+//   H[X_i,t_c] = B_ic = Q_ci^T hat(n_ci)
+//   H[t,t]     = T = blockdiag_c(sum_i hat(n_ci)^T hat(n_ci)) + coplanarity rows (:36-47), dense 3C x 3C
+// The reference takes scipy.linalg.eigh(H)[0:6] and uses the 4 smallest eigenvectors (:96-107).  Here the 6
+// smallest eigenpairs come from inverse subspace iteration with Rayleigh-Ritz; (H + sigma I)^-1 is applied
+// by eliminating the X blocks (Schur complement S = T + sigma I - sum_i B_i^T (D_i + sigma I)^-1 B_i, 3C x 3C).
+// All O(M) work runs in kernels; the 3C x 3C Cholesky and the 6 x 6 Ritz problem are host scalar logic.
+#include "rsx_handle.cuh"
+#include "rsx_fit.cuh"
+#include <vector>
+#include <stdlib.h>
+
+#define KB 6   // block size of the subspace iteration (the reference asks LAPACK for 6 eigenpairs)
+
+int bax_syrk(bax_handle* h, const double* X, int rows, int64_t K, int64_t ldx, double* out, cudaStream_t s);
+
+// ------------------------------------------------------------------ rotation part
+// Xt[3c+d][i] = v[c][idx[i]][d]   (rows contiguous over the selected directions; SYRK gives V^T V)
+__global__ void k_gather_dirs(const double* __restrict__ v, const int32_t* __restrict__ idx, int C, int64_t N,
+                              int64_t Nin, int64_t ld, double* __restrict__ Xt) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Nin) return;
+  const int64_t src = idx[i];
+  for (int c = 0; c < C; ++c)
+    for (int d = 0; d < 3; ++d) Xt[(size_t)(3 * c + d) * ld + i] = v[((size_t)c * N + src) * 3 + d];
+}
+
+// single CTA: eigenvectors of the 3C x 3C Gram matrix, R_c = (inv(A_0) A_c)^T with A = top-3 eigenvectors^T
+__global__ void __launch_bounds__(256)
+k_rsx_rot(const double* __restrict__ Gm, int C, double* __restrict__ ws /*global A,V if too big for smem*/,
+          double* __restrict__ R_out) {
+  extern __shared__ __align__(16) double sm[];
+  const int n = 3 * C, ld = n | 1;
+  double* A = ws ? ws : sm;
+  double* V = A + (size_t)n * ld;
+  double* cs = ws ? sm : V + (size_t)n * ld;
+  int* flag = (int*)(cs + 2 * (n / 2 + 1));
+  CtaCtx g{(int)threadIdx.x, (int)blockDim.x};
+  for (int idx = threadIdx.x; idx < n * n; idx += blockDim.x) A[(idx / n) * ld + idx % n] = Gm[idx];
+  __syncthreads();
+  cta_jacobi(g, A, V, n, ld, cs, flag, 60);
+  __shared__ int top[3];
+  if (threadIdx.x == 0) {
+    for (int pass = 0; pass < 3; ++pass) {
+      int bi = -1; double bv = 0;
+      for (int i = 0; i < n; ++i) {
+        bool used = false;
+        for (int q = 0; q < pass; ++q) used |= (top[q] == i);
+        if (used) continue;
+        if (bi < 0 || A[i * ld + i] > bv) { bi = i; bv = A[i * ld + i]; }
+      }
+      top[pass] = bi;
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    double A0[9], Ac[9], inv0[9];
+    for (int r = 0; r < 3; ++r)
+      for (int d = 0; d < 3; ++d) { A0[3 * r + d] = V[d * ld + top[r]]; Ac[3 * r + d] = V[(3 * c + d) * ld + top[r]]; }
+    inv3(A0, inv0);
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) {
+        double acc = 0.0;
+        for (int k = 0; k < 3; ++k) acc += inv0[3 * j + k] * Ac[3 * k + i];
+        R_out[9 * c + 3 * i + j] = acc;
+      }
+  }
+}
+
+// ------------------------------------------------------------------ translation part
+__device__ __forceinline__ void load_ray(const double* __restrict__ n, const int32_t* __restrict__ idx, int64_t M,
+                                         int c, int64_t i, double* nn) {
+  const double* p = n + ((size_t)c * M + idx[i]) * 3;
+  nn[0] = p[0]; nn[1] = p[1]; nn[2] = p[2];
+}
+
+// T blocks.  task < C: diagonal collinearity block sum_i hat(n)^T hat(n) of camera `task` (6 sums);
+// task >= C: camera pair (a < b): sum_i of ra ra^T (6), rb rb^T (6), ra rb^T (9), ra = R_a m, rb = -R_b m,
+// m = (R_a^T n_ai) x (R_b^T n_bi).  One CTA per (task, chunk of points); partial sums [chunk][task][21].
+__global__ void __launch_bounds__(256)
+k_arrow_T(const double* __restrict__ n, const int32_t* __restrict__ idx, int C, int64_t M, int64_t Min,
+          const double* __restrict__ R, int64_t chunk, double* __restrict__ part) {
+  __shared__ double red[21 * 32];
+  const int task = blockIdx.x;
+  const int64_t i0 = (int64_t)blockIdx.y * chunk;
+  int64_t i1 = i0 + chunk; if (i1 > Min) i1 = Min;
+  double acc[21];
+#pragma unroll
+  for (int e = 0; e < 21; ++e) acc[e] = 0.0;
+  if (task < C) {
+    for (int64_t i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+      double nn[3]; load_ray(n, idx, M, task, i, nn);
+      const double Nx[9] = {0, -nn[2], nn[1], nn[2], 0, -nn[0], -nn[1], nn[0], 0};
+      int e = 0;
+#pragma unroll
+      for (int p = 0; p < 3; ++p)
+#pragma unroll
+        for (int q = p; q < 3; ++q) { acc[e] += Nx[p] * Nx[q] + Nx[3 + p] * Nx[3 + q] + Nx[6 + p] * Nx[6 + q]; ++e; }
+    }
+  } else {
+    int t = task - C, a = 0;
+    while (t >= C - 1 - a) { t -= C - 1 - a; ++a; }
+    const int b = a + 1 + t;
+    double Ra[9], Rb[9];
+    for (int e = 0; e < 9; ++e) { Ra[e] = R[9 * a + e]; Rb[e] = R[9 * b + e]; }
+    for (int64_t i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+      double na[3], nb[3], wa[3], wb[3], m[3], ra[3], rb[3];
+      load_ray(n, idx, M, a, i, na); load_ray(n, idx, M, b, i, nb);
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        wa[j] = Ra[j] * na[0] + Ra[3 + j] * na[1] + Ra[6 + j] * na[2];
+        wb[j] = Rb[j] * nb[0] + Rb[3 + j] * nb[1] + Rb[6 + j] * nb[2];
+      }
+      cross3(wa, wb, m);
+#pragma unroll
+      for (int p = 0; p < 3; ++p) {
+        ra[p] = Ra[3 * p] * m[0] + Ra[3 * p + 1] * m[1] + Ra[3 * p + 2] * m[2];
+        rb[p] = -(Rb[3 * p] * m[0] + Rb[3 * p + 1] * m[1] + Rb[3 * p + 2] * m[2]);
+      }
+      int e = 0;
+#pragma unroll
+      for (int p = 0; p < 3; ++p)
+#pragma unroll
+        for (int q = p; q < 3; ++q) { acc[e] += ra[p] * ra[q]; acc[6 + e] += rb[p] * rb[q]; ++e; }
+#pragma unroll
+      for (int p = 0; p < 3; ++p)
+#pragma unroll
+        for (int q = 0; q < 3; ++q) acc[12 + 3 * p + q] += ra[p] * rb[q];
+    }
+  }
+  block_sum<21>(acc, red);
+  if (threadIdx.x == 0) {
+    double* o = part + ((size_t)blockIdx.y * gridDim.x + task) * 21;
+    for (int e = 0; e < 21; ++e) o[e] = acc[e];
+  }
+}
+
+// per point: D_i (packed xx,xy,xz,yy,yz,zz), Bt[a][3i+j] = B_i[j][a], Yw[a][3i+j] = (L_i^-1 B_i)[j][a],
+// L_i L_i^T = D_i + sigma I
+__global__ void __launch_bounds__(128)
+k_arrow_prep(const double* __restrict__ n, const int32_t* __restrict__ idx, int C, int64_t M, int64_t Min,
+             const double* __restrict__ R, double sigma, double* __restrict__ D, double* __restrict__ Bt,
+             double* __restrict__ Yw, int64_t ldq) {
+  extern __shared__ double sR[];
+  for (int e = threadIdx.x; e < 9 * C; e += blockDim.x) sR[e] = R[e];
+  __syncthreads();
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Min) return;
+  double Dp[6] = {0, 0, 0, 0, 0, 0};
+  for (int c = 0; c < C; ++c) {
+    double nn[3], Q[9]; load_ray(n, idx, M, c, i, nn);
+    hatmul(nn, sR + 9 * c, Q);
+    Dp[0] += Q[0] * Q[0] + Q[3] * Q[3] + Q[6] * Q[6]; Dp[1] += Q[0] * Q[1] + Q[3] * Q[4] + Q[6] * Q[7];
+    Dp[2] += Q[0] * Q[2] + Q[3] * Q[5] + Q[6] * Q[8]; Dp[3] += Q[1] * Q[1] + Q[4] * Q[4] + Q[7] * Q[7];
+    Dp[4] += Q[1] * Q[2] + Q[4] * Q[5] + Q[7] * Q[8]; Dp[5] += Q[2] * Q[2] + Q[5] * Q[5] + Q[8] * Q[8];
+  }
+#pragma unroll
+  for (int e = 0; e < 6; ++e) D[6 * i + e] = Dp[e];
+  const Chol3 L = chol3(Dp, sigma);
+  for (int c = 0; c < C; ++c) {
+    double nn[3], Q[9]; load_ray(n, idx, M, c, i, nn);
+    hatmul(nn, sR + 9 * c, Q);
+    const double Nx[9] = {0, -nn[2], nn[1], nn[2], 0, -nn[0], -nn[1], nn[0], 0};
+#pragma unroll
+    for (int b = 0; b < 3; ++b) {
+      double w0 = Q[0] * Nx[b] + Q[3] * Nx[3 + b] + Q[6] * Nx[6 + b];      // column b of Q^T hat(n)
+      double w1 = Q[1] * Nx[b] + Q[4] * Nx[3 + b] + Q[7] * Nx[6 + b];
+      double w2 = Q[2] * Nx[b] + Q[5] * Nx[3 + b] + Q[8] * Nx[6 + b];
+      double* o = Bt + (size_t)(3 * c + b) * ldq + 3 * i;
+      o[0] = w0; o[1] = w1; o[2] = w2;
+      chol3_fwd(L, w0, w1, w2);
+      double* y = Yw + (size_t)(3 * c + b) * ldq + 3 * i;
+      y[0] = w0; y[1] = w1; y[2] = w2;
+    }
+  }
+}
+
+// mode 0: Y_i <- (D_i + sigma I)^-1 Z_i                                  (forward half of the block solve)
+// mode 1: Y_i <- Y_i - (D_i + sigma I)^-1 (B_i t)                        (backward half)
+// mode 2: W_i <- D_i Y_i + B_i t                                         (X rows of H [Y; t])
+__global__ void __launch_bounds__(128)
+k_arrow_point(int mode, int C, int64_t Min, double sigma, const double* __restrict__ D, const double* __restrict__ Bt,
+              int64_t ldq, const double* __restrict__ tv /*[3C][KB]*/, double* __restrict__ Y /*[Min][3][KB]*/,
+              double* __restrict__ W) {
+  extern __shared__ double st[];
+  if (mode) { for (int e = threadIdx.x; e < 3 * C * KB; e += blockDim.x) st[e] = tv[e]; }
+  __syncthreads();
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Min) return;
+  double Dp[6];
+#pragma unroll
+  for (int e = 0; e < 6; ++e) Dp[e] = D[6 * i + e];
+  double bt[3][KB];
+  if (mode) {
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+#pragma unroll
+      for (int k = 0; k < KB; ++k) bt[j][k] = 0.0;
+    for (int a = 0; a < 3 * C; ++a) {
+      const double* bp = Bt + (size_t)a * ldq + 3 * i;
+      const double b0 = bp[0], b1 = bp[1], b2 = bp[2];
+#pragma unroll
+      for (int k = 0; k < KB; ++k) { const double t = st[a * KB + k]; bt[0][k] += b0 * t; bt[1][k] += b1 * t; bt[2][k] += b2 * t; }
+    }
+  }
+  double* y = Y + (size_t)i * 3 * KB;
+  if (mode == 2) {
+    double* w = W + (size_t)i * 3 * KB;
+#pragma unroll
+    for (int k = 0; k < KB; ++k) {
+      const double y0 = y[k], y1 = y[KB + k], y2 = y[2 * KB + k];
+      w[k] = Dp[0] * y0 + Dp[1] * y1 + Dp[2] * y2 + bt[0][k];
+      w[KB + k] = Dp[1] * y0 + Dp[3] * y1 + Dp[4] * y2 + bt[1][k];
+      w[2 * KB + k] = Dp[2] * y0 + Dp[4] * y1 + Dp[5] * y2 + bt[2][k];
+    }
+    return;
+  }
+  const Chol3 L = chol3(Dp, sigma);
+#pragma unroll
+  for (int k = 0; k < KB; ++k) {
+    double a0, a1, a2;
+    if (mode == 0) { a0 = y[k]; a1 = y[KB + k]; a2 = y[2 * KB + k]; }
+    else { a0 = bt[0][k]; a1 = bt[1][k]; a2 = bt[2][k]; }
+    chol3_fwd(L, a0, a1, a2); chol3_bwd(L, a0, a1, a2);
+    if (mode == 0) { y[k] = a0; y[KB + k] = a1; y[2 * KB + k] = a2; }
+    else { y[k] -= a0; y[KB + k] -= a1; y[2 * KB + k] -= a2; }
+  }
+}
+
+// out[a][k] = sum_q Bt[a][q] Y[q][k]  (q = 3 i + j): one CTA per (a, chunk of q), partial [chunk][3C][KB]
+__global__ void __launch_bounds__(256)
+k_arrow_bty(const double* __restrict__ Bt, int64_t ldq, int64_t Q, int64_t chunk, int rows,
+            const double* __restrict__ Y, double* __restrict__ part) {
+  __shared__ double red[KB * 32];
+  const int a = blockIdx.x;
+  const int64_t q0 = (int64_t)blockIdx.y * chunk;
+  int64_t q1 = q0 + chunk; if (q1 > Q) q1 = Q;
+  double acc[KB];
+#pragma unroll
+  for (int k = 0; k < KB; ++k) acc[k] = 0.0;
+  for (int64_t q = q0 + threadIdx.x; q < q1; q += blockDim.x) {
+    const double b = Bt[(size_t)a * ldq + q];
+#pragma unroll
+    for (int k = 0; k < KB; ++k) acc[k] += b * Y[q * KB + k];
+  }
+  block_sum<KB>(acc, red);
+  if (threadIdx.x == 0)
+    for (int k = 0; k < KB; ++k) part[((size_t)blockIdx.y * rows + a) * KB + k] = acc[k];
+}
+
+// Gram sums over the X rows: [0..35] Y^T Y, [36..71] Y^T W   (row-major KB x KB each)
+__global__ void __launch_bounds__(256)
+k_arrow_gram(int64_t Q, const double* __restrict__ Y, const double* __restrict__ W, double* __restrict__ part) {
+  __shared__ double red[2 * KB * KB * 32];
+  double acc[2 * KB * KB];
+#pragma unroll
+  for (int e = 0; e < 2 * KB * KB; ++e) acc[e] = 0.0;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < Q; q += (int64_t)gridDim.x * blockDim.x) {
+    double y[KB], w[KB];
+#pragma unroll
+    for (int k = 0; k < KB; ++k) { y[k] = Y[q * KB + k]; w[k] = W[q * KB + k]; }
+#pragma unroll
+    for (int k = 0; k < KB; ++k)
+#pragma unroll
+      for (int l = 0; l < KB; ++l) { acc[k * KB + l] += y[k] * y[l]; acc[KB * KB + k * KB + l] += y[k] * w[l]; }
+  }
+  block_sum<2 * KB * KB>(acc, red);
+  if (threadIdx.x == 0)
+    for (int e = 0; e < 2 * KB * KB; ++e) part[(size_t)blockIdx.x * 2 * KB * KB + e] = acc[e];
+}
+
+// Y <- Y Cm, W <- W Cm; partial sums of |W_k - theta_k Y_k|^2 over the X rows
+__global__ void __launch_bounds__(256)
+k_arrow_mix(int64_t Q, const double* __restrict__ cm /*[KB][KB] then theta [KB]*/, double* __restrict__ Y,
+            double* __restrict__ W /*may be null*/, double* __restrict__ part) {
+  __shared__ double red[KB * 32];
+  __shared__ double sc[KB * KB + KB];
+  if (threadIdx.x < KB * KB + KB) sc[threadIdx.x] = cm[threadIdx.x];
+  __syncthreads();
+  double acc[KB];
+#pragma unroll
+  for (int k = 0; k < KB; ++k) acc[k] = 0.0;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < Q; q += (int64_t)gridDim.x * blockDim.x) {
+    double y[KB], w[KB];
+#pragma unroll
+    for (int k = 0; k < KB; ++k) { y[k] = Y[q * KB + k]; w[k] = W ? W[q * KB + k] : 0.0; }
+#pragma unroll
+    for (int l = 0; l < KB; ++l) {
+      double yn = 0.0, wn = 0.0;
+#pragma unroll
+      for (int k = 0; k < KB; ++k) { yn += y[k] * sc[k * KB + l]; wn += w[k] * sc[k * KB + l]; }
+      Y[q * KB + l] = yn;
+      if (W) W[q * KB + l] = wn;
+      const double r = wn - sc[KB * KB + l] * yn;
+      acc[l] += r * r;
+    }
+  }
+  block_sum<KB>(acc, red);
+  if (threadIdx.x == 0)
+    for (int k = 0; k < KB; ++k) part[(size_t)blockIdx.x * KB + k] = acc[k];
+}
+
+// X_i = sign/s * (Y_i[:, 0:4] c4); z-test counts over every selected ray with both signs (util.py:161-180)
+__global__ void __launch_bounds__(128)
+k_arrow_finish(const double* __restrict__ n, const int32_t* __restrict__ idx, int64_t M, int64_t Min,
+               const double* __restrict__ Rt01 /*[2][12] with +t*/, const double* __restrict__ c4s /*[4] = c4 / s*/,
+               const double* __restrict__ Y, double* __restrict__ Xout, unsigned long long* __restrict__ counts) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long zp = 0, zn = 0;
+  if (i < Min) {
+    if (Xout) {
+      const double* y = Y + (size_t)i * 3 * KB;
+      for (int j = 0; j < 3; ++j)
+        Xout[3 * i + j] = y[j * KB] * c4s[0] + y[j * KB + 1] * c4s[1] + y[j * KB + 2] * c4s[2] + y[j * KB + 3] * c4s[3];
+    }
+    double n0[3], n1[3];
+    load_ray(n, idx, M, 0, i, n0); load_ray(n, idx, M, 1, i, n1);
+    for (int sgi = 0; sgi < 2; ++sgi) {
+      const double sg = sgi ? -1.0 : 1.0;
+      double P0[12], P1[12];
+      for (int e = 0; e < 12; ++e) { const bool tcol = (e & 3) == 3; P0[e] = tcol ? sg * Rt01[e] : Rt01[e]; P1[e] = tcol ? sg * Rt01[12 + e] : Rt01[12 + e]; }
+      double m[10];
+      for (int e = 0; e < 10; ++e) m[e] = 0.0;
+      dlt_accumulate(P0, n0[0], n0[1], m);
+      dlt_accumulate(P1, n1[0], n1[1], m);
+      double a[4][4], X[4];
+      sym10_to_full(m, a);
+      eig4_smallest(a, X);
+      const double x0 = X[0] / X[3], x1 = X[1] / X[3], x2 = X[2] / X[3];
+      const double z0 = Rt01[8] * x0 + Rt01[9] * x1 + Rt01[10] * x2 + Rt01[11];
+      const double z1 = Rt01[20] * x0 + Rt01[21] * x1 + Rt01[22] * x2 + Rt01[23];
+      const unsigned long long cnt = (z0 > 0 ? 1 : 0) + (z1 > 0 ? 1 : 0);
+      if (sgi) zn += cnt; else zp += cnt;
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) { zp += __shfl_xor_sync(0xffffffffu, zp, o); zn += __shfl_xor_sync(0xffffffffu, zn, o); }
+  if ((threadIdx.x & 31) == 0) { if (zp) atomicAdd(counts, zp); if (zn) atomicAdd(counts + 1, zn); }
+}
+__global__ void k_scale_X(double* __restrict__ X, int64_t n3, double f) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n3) X[i] *= f;
+}
+
+// ------------------------------------------------------------------ host driver
+namespace {
+struct DevBuf {
+  void* p = nullptr;
+  ~DevBuf() { if (p) cudaFree(p); }
+  cudaError_t alloc(size_t bytes, bool zero, cudaStream_t s) {
+    cudaError_t e = cudaMalloc(&p, bytes ? bytes : 8);
+    if (e == cudaSuccess && zero) e = cudaMemsetAsync(p, 0, bytes ? bytes : 8, s);
+    return e;
+  }
+  double* d() const { return (double*)p; }
+};
+
+// symmetric eigen-decomposition of a small dense matrix on the host (same Jacobi code as the device path)
+void host_eigh(int n, std::vector<double>& A /*n*n in, destroyed*/, std::vector<double>& w, std::vector<double>& V) {
+  const int ld = n | 1;
+  std::vector<double> a((size_t)n * ld), v((size_t)n * ld), cs(2 * (n / 2 + 1));
+  int flag[2];
+  for (int i = 0; i < n; ++i) for (int j = 0; j < n; ++j) a[i * ld + j] = 0.5 * (A[i * n + j] + A[j * n + i]);
+  CtaCtx g{0, 1};
+  cta_jacobi(g, a.data(), v.data(), n, ld, cs.data(), flag, 60);
+  std::vector<int> order(n);
+  for (int i = 0; i < n; ++i) order[i] = i;
+  for (int i = 0; i < n; ++i) for (int j = i + 1; j < n; ++j) if (a[order[j] * ld + order[j]] < a[order[i] * ld + order[i]]) { int t = order[i]; order[i] = order[j]; order[j] = t; }
+  w.resize(n); V.assign((size_t)n * n, 0.0);
+  for (int k = 0; k < n; ++k) { w[k] = a[order[k] * ld + order[k]]; for (int i = 0; i < n; ++i) V[i * n + k] = v[i * ld + order[k]]; }
+}
+bool host_cholesky(int n, std::vector<double>& A) {     // in place, lower, row-major
+  for (int k = 0; k < n; ++k) {
+    double d = A[k * n + k];
+    for (int j = 0; j < k; ++j) d -= A[k * n + j] * A[k * n + j];
+    if (!(d > 0)) return false;
+    d = sqrt(d); A[k * n + k] = d;
+    for (int i = k + 1; i < n; ++i) {
+      double s = A[i * n + k];
+      for (int j = 0; j < k; ++j) s -= A[i * n + j] * A[k * n + j];
+      A[i * n + k] = s / d;
+    }
+  }
+  return true;
+}
+void host_chol_solve(int n, const std::vector<double>& L, double* x, int stride) {   // x[i*stride]
+  for (int i = 0; i < n; ++i) { double s = x[i * stride]; for (int j = 0; j < i; ++j) s -= L[i * n + j] * x[j * stride]; x[i * stride] = s / L[i * n + i]; }
+  for (int i = n - 1; i >= 0; --i) { double s = x[i * stride]; for (int j = i + 1; j < n; ++j) s -= L[j * n + i] * x[j * stride]; x[i * stride] = s / L[i * n + i]; }
+}
+}  // namespace
+
+#define RSX_CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { bax_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); return BAX_E_CUDA; } } while (0)
+
+extern "C" int rsx_calib_linear(rsx_handle* h, const uint8_t* mask3d, const uint8_t* mask2d, double* Rt_out, double* X_out,
+                                int64_t* info_host, void* stream) {
+  if (!h || !h->v || !Rt_out) { bax_set_error("rsx_calib_linear: bad argument / no problem"); return BAX_E_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  RSX_CU(cudaSetDevice(h->device));
+  const int C = h->C, n3 = 3 * C;
+  const int64_t N = h->N, M = h->M;
+  // ---- 1. index lists of the selected directions / rays
+  std::vector<int32_t> iv, im;
+  {
+    std::vector<uint8_t> m3(N, 1), m2(M, 1);
+    if (mask3d) RSX_CU(cudaMemcpyAsync(m3.data(), mask3d, N, cudaMemcpyDeviceToHost, s));
+    if (mask2d) RSX_CU(cudaMemcpyAsync(m2.data(), mask2d, M, cudaMemcpyDeviceToHost, s));
+    RSX_CU(cudaStreamSynchronize(s));
+    for (int64_t i = 0; i < N; ++i) if (m3[i]) iv.push_back((int32_t)i);
+    for (int64_t i = 0; i < M; ++i) if (m2[i]) im.push_back((int32_t)i);
+  }
+  const int64_t Nin = (int64_t)iv.size(), Min = (int64_t)im.size();
+  if (info_host) { info_host[0] = Min; info_host[1] = Nin; info_host[2] = 0; info_host[3] = 0; }
+  if (Nin < 3 || Min < 2) { bax_set_error("rsx_calib_linear: %lld directions / %lld rays selected, too few", (long long)Nin, (long long)Min); return BAX_E_NUMERIC; }
+  DevBuf d_iv, d_im;
+  RSX_CU(d_iv.alloc(sizeof(int32_t) * Nin, false, s)); RSX_CU(d_im.alloc(sizeof(int32_t) * Min, false, s));
+  RSX_CU(cudaMemcpyAsync(d_iv.p, iv.data(), sizeof(int32_t) * Nin, cudaMemcpyHostToDevice, s));
+  RSX_CU(cudaMemcpyAsync(d_im.p, im.data(), sizeof(int32_t) * Min, cudaMemcpyHostToDevice, s));
+  const int32_t* idx_v = (const int32_t*)d_iv.p; const int32_t* idx_m = (const int32_t*)d_im.p;
+  RsxTimer timer(h, RSX_T_FINAL, s, 0);
+  // ---- 2. rotations
+  DevBuf d_R;
+  RSX_CU(d_R.alloc(sizeof(double) * 9 * C, false, s));
+  {
+    const int64_t ldn = ((Nin + 31) / 32) * 32;
+    DevBuf d_Xt, d_G, d_ws;
+    RSX_CU(d_Xt.alloc(sizeof(double) * n3 * ldn, true, s)); RSX_CU(d_G.alloc(sizeof(double) * n3 * n3, false, s));
+    k_gather_dirs<<<(unsigned)((Nin + 255) / 256), 256, 0, s>>>(h->v, idx_v, C, N, Nin, ldn, d_Xt.d());
+    RSX_CU(cudaGetLastError());
+    int rc = bax_syrk(h->bx, d_Xt.d(), n3, Nin, ldn, d_G.d(), s); if (rc) return rc;
+    const int ld = n3 | 1;
+    size_t small = sizeof(double) * (2 * (n3 / 2 + 1) + 2), big = sizeof(double) * 2 * (size_t)n3 * ld;
+    size_t smem = small + big;
+    double* ws = nullptr;
+    if (smem > 200 * 1024) { RSX_CU(d_ws.alloc(big, false, s)); ws = d_ws.d(); smem = small; }
+    RSX_CU(cudaFuncSetAttribute(k_rsx_rot, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_rsx_rot<<<1, 256, smem, s>>>(d_G.d(), C, ws, d_R.d());
+    RSX_CU(cudaGetLastError());
+    RSX_CU(cudaStreamSynchronize(s));
+    h->t_launch[RSX_T_FINAL] += 4;
+  }
+  std::vector<double> Rh(9 * C);
+  RSX_CU(cudaMemcpyAsync(Rh.data(), d_R.p, sizeof(double) * 9 * C, cudaMemcpyDeviceToHost, s));
+  // ---- 3. T (3C x 3C)
+  const int ntask = C + C * (C - 1) / 2;
+  std::vector<double> T((size_t)n3 * n3, 0.0);
+  {
+    int nchunk = (int)((Min + 1023) / 1024); if (nchunk > 16) nchunk = 16; if (nchunk < 1) nchunk = 1;
+    const int64_t chunk = (Min + nchunk - 1) / nchunk;
+    DevBuf d_part, d_sum;
+    RSX_CU(d_part.alloc(sizeof(double) * (size_t)nchunk * ntask * 21, false, s)); RSX_CU(d_sum.alloc(sizeof(double) * ntask * 21, false, s));
+    k_arrow_T<<<dim3(ntask, nchunk), 256, 0, s>>>(h->n, idx_m, C, M, Min, d_R.d(), chunk, d_part.d());
+    RSX_CU(cudaGetLastError());
+    int rc = bax_reduce_partials(h->bx, d_part.d(), nchunk, ntask * 21, d_sum.d(), s); if (rc) return rc;
+    std::vector<double> ts((size_t)ntask * 21);
+    RSX_CU(cudaMemcpyAsync(ts.data(), d_sum.p, sizeof(double) * ntask * 21, cudaMemcpyDeviceToHost, s));
+    RSX_CU(cudaStreamSynchronize(s));
+    h->t_launch[RSX_T_FINAL] += 2;
+    auto add_sym = [&](int c, const double* a6) {
+      int e = 0;
+      for (int p = 0; p < 3; ++p) for (int q = p; q < 3; ++q) { T[(3 * c + p) * n3 + 3 * c + q] += a6[e]; if (p != q) T[(3 * c + q) * n3 + 3 * c + p] += a6[e]; ++e; }
+    };
+    for (int c = 0; c < C; ++c) add_sym(c, &ts[(size_t)c * 21]);
+    int task = C;
+    for (int a = 0; a < C; ++a) for (int b = a + 1; b < C; ++b, ++task) {
+      const double* a21 = &ts[(size_t)task * 21];
+      add_sym(a, a21); add_sym(b, a21 + 6);
+      for (int p = 0; p < 3; ++p) for (int q = 0; q < 3; ++q) { T[(3 * a + p) * n3 + 3 * b + q] += a21[12 + 3 * p + q]; T[(3 * b + q) * n3 + 3 * a + p] += a21[12 + 3 * p + q]; }
+    }
+  }
+  double scale = 0; for (int i = 0; i < n3; ++i) scale += T[i * n3 + i]; scale /= n3;
+  const double sigma = 1e-10 * scale;
+  // ---- 4. per-point blocks, Schur complement
+  const int64_t Q = 3 * Min, ldq = ((Q + 31) / 32) * 32;
+  DevBuf d_D, d_Bt, d_Yw, d_YY, d_Y, d_W, d_tv, d_part, d_out, d_cm;
+  RSX_CU(d_D.alloc(sizeof(double) * 6 * Min, false, s));
+  RSX_CU(d_Bt.alloc(sizeof(double) * n3 * ldq, true, s)); RSX_CU(d_Yw.alloc(sizeof(double) * n3 * ldq, true, s));
+  RSX_CU(d_YY.alloc(sizeof(double) * n3 * n3, false, s));
+  const int nbp = (int)((Min + 127) / 128);
+  k_arrow_prep<<<nbp, 128, sizeof(double) * 9 * C, s>>>(h->n, idx_m, C, M, Min, d_R.d(), sigma, d_D.d(), d_Bt.d(), d_Yw.d(), ldq);
+  RSX_CU(cudaGetLastError());
+  { int rc = bax_syrk(h->bx, d_Yw.d(), n3, Q, ldq, d_YY.d(), s); if (rc) return rc; }
+  std::vector<double> S((size_t)n3 * n3);
+  RSX_CU(cudaMemcpyAsync(S.data(), d_YY.p, sizeof(double) * n3 * n3, cudaMemcpyDeviceToHost, s));
+  RSX_CU(cudaStreamSynchronize(s));
+  h->t_launch[RSX_T_FINAL] += 3;
+  for (int i = 0; i < n3; ++i) for (int j = 0; j < n3; ++j) S[i * n3 + j] = T[i * n3 + j] - S[i * n3 + j] + (i == j ? sigma : 0.0);
+  if (!host_cholesky(n3, S)) { bax_set_error("rsx_calib_linear: reduced translation system is not positive definite"); return BAX_E_NUMERIC; }
+  // ---- 5. inverse subspace iteration with Rayleigh-Ritz
+  RSX_CU(d_Y.alloc(sizeof(double) * Q * KB, false, s)); RSX_CU(d_W.alloc(sizeof(double) * Q * KB, false, s));
+  RSX_CU(d_tv.alloc(sizeof(double) * n3 * KB, false, s)); RSX_CU(d_cm.alloc(sizeof(double) * (KB * KB + KB), false, s));
+  int nchq = (int)((Q + 8191) / 8192); if (nchq > 64) nchq = 64; if (nchq < 1) nchq = 1;
+  const int64_t chq = (Q + nchq - 1) / nchq;
+  int ggrid = (int)((Q + 255) / 256); if (ggrid > 2 * h->sm_count) ggrid = 2 * h->sm_count;
+  size_t part_d = (size_t)nchq * n3 * KB; if (part_d < (size_t)ggrid * 2 * KB * KB) part_d = (size_t)ggrid * 2 * KB * KB;
+  RSX_CU(d_part.alloc(sizeof(double) * part_d, false, s)); RSX_CU(d_out.alloc(sizeof(double) * (n3 * KB + 2 * KB * KB), false, s));
+  std::vector<double> yx((size_t)Q * KB), yt((size_t)n3 * KB), wt((size_t)n3 * KB), tmp((size_t)n3 * KB), red(2 * KB * KB + n3 * KB);
+  {
+    uint64_t st = 0x9E3779B97F4A7C15ULL;      // fixed start: the result does not depend on it once converged
+    auto rnd = [&]() { st ^= st << 13; st ^= st >> 7; st ^= st << 17; return (double)(st >> 11) * (1.0 / 9007199254740992.0) - 0.5; };
+    for (auto& x : yx) x = rnd();
+    for (auto& x : yt) x = rnd();
+  }
+  RSX_CU(cudaMemcpyAsync(d_Y.p, yx.data(), sizeof(double) * Q * KB, cudaMemcpyHostToDevice, s));
+  const size_t sm_pt = sizeof(double) * n3 * KB;
+  auto bty = [&](const double* Yd, double* host_out) -> int {       // host_out[a*KB+k] = sum_q Bt[a][q] Y[q][k]
+    k_arrow_bty<<<dim3(n3, nchq), 256, 0, s>>>(d_Bt.d(), ldq, Q, chq, n3, Yd, d_part.d());
+    if (cudaGetLastError() != cudaSuccess) return BAX_E_CUDA;
+    int rc = bax_reduce_partials(h->bx, d_part.d(), nchq, n3 * KB, d_out.d(), s); if (rc) return rc;
+    if (cudaMemcpyAsync(host_out, d_out.p, sizeof(double) * n3 * KB, cudaMemcpyDeviceToHost, s) != cudaSuccess) return BAX_E_CUDA;
+    if (cudaStreamSynchronize(s) != cudaSuccess) return BAX_E_CUDA;
+    h->t_launch[RSX_T_FINAL] += 2;
+    return BAX_OK;
+  };
+  auto gram = [&](const double* Yd, const double* Wd, double* host72) -> int {
+    k_arrow_gram<<<ggrid, 256, 0, s>>>(Q, Yd, Wd, d_part.d());
+    if (cudaGetLastError() != cudaSuccess) return BAX_E_CUDA;
+    int rc = bax_reduce_partials(h->bx, d_part.d(), ggrid, 2 * KB * KB, d_out.d(), s); if (rc) return rc;
+    if (cudaMemcpyAsync(host72, d_out.p, sizeof(double) * 2 * KB * KB, cudaMemcpyDeviceToHost, s) != cudaSuccess) return BAX_E_CUDA;
+    if (cudaStreamSynchronize(s) != cudaSuccess) return BAX_E_CUDA;
+    h->t_launch[RSX_T_FINAL] += 2;
+    return BAX_OK;
+  };
+  auto mix = [&](const double* cm42, bool with_w, double* host_res6) -> int {
+    if (cudaMemcpyAsync(d_cm.p, cm42, sizeof(double) * (KB * KB + KB), cudaMemcpyHostToDevice, s) != cudaSuccess) return BAX_E_CUDA;
+    k_arrow_mix<<<ggrid, 256, 0, s>>>(Q, d_cm.d(), d_Y.d(), with_w ? d_W.d() : nullptr, d_part.d());
+    if (cudaGetLastError() != cudaSuccess) return BAX_E_CUDA;
+    int rc = bax_reduce_partials(h->bx, d_part.d(), ggrid, KB, d_out.d(), s); if (rc) return rc;
+    if (cudaMemcpyAsync(host_res6, d_out.p, sizeof(double) * KB, cudaMemcpyDeviceToHost, s) != cudaSuccess) return BAX_E_CUDA;
+    if (cudaStreamSynchronize(s) != cudaSuccess) return BAX_E_CUDA;
+    h->t_launch[RSX_T_FINAL] += 2;
+    return BAX_OK;
+  };
+  auto mix_host = [&](std::vector<double>& A, const double* cm) {     // A [n3][KB] <- A cm
+    for (int a = 0; a < n3; ++a) {
+      double r[KB];
+      for (int l = 0; l < KB; ++l) { r[l] = 0; for (int k = 0; k < KB; ++k) r[l] += A[a * KB + k] * cm[k * KB + l]; }
+      for (int l = 0; l < KB; ++l) A[a * KB + l] = r[l];
+    }
+  };
+  int it = 0, converged = 0, rc = BAX_OK;
+  double theta[KB] = {0};
+  const int max_it = 80;
+  for (; it < max_it && !converged; ++it) {
+    // (H + sigma I)^-1 [Y; yt]
+    k_arrow_point<<<nbp, 128, sm_pt, s>>>(0, C, Min, sigma, d_D.d(), d_Bt.d(), ldq, d_tv.d(), d_Y.d(), nullptr);
+    if ((rc = bty(d_Y.d(), tmp.data()))) return rc;
+    for (int e = 0; e < n3 * KB; ++e) yt[e] -= tmp[e];
+    for (int k = 0; k < KB; ++k) host_chol_solve(n3, S, yt.data() + k, KB);
+    RSX_CU(cudaMemcpyAsync(d_tv.p, yt.data(), sizeof(double) * n3 * KB, cudaMemcpyHostToDevice, s));
+    k_arrow_point<<<nbp, 128, sm_pt, s>>>(1, C, Min, sigma, d_D.d(), d_Bt.d(), ldq, d_tv.d(), d_Y.d(), nullptr);
+    RSX_CU(cudaGetLastError());
+    h->t_launch[RSX_T_FINAL] += 2;
+    // orthonormalise [Y; yt] (shifted whitening passes: Gram -> eigen-decomposition -> Y <- Y U L^-1/2)
+    for (int pass = 0; pass < 5; ++pass) {
+      if ((rc = gram(d_Y.d(), d_Y.d(), red.data()))) return rc;
+      std::vector<double> Gm(KB * KB), w, U;
+      for (int k = 0; k < KB; ++k) for (int l = 0; l < KB; ++l) { double a = red[k * KB + l]; for (int q = 0; q < n3; ++q) a += yt[q * KB + k] * yt[q * KB + l]; Gm[k * KB + l] = a; }
+      double dn[KB], dev = 0;
+      for (int k = 0; k < KB; ++k) dn[k] = 1.0 / sqrt(Gm[k * KB + k]);
+      for (int k = 0; k < KB; ++k) for (int l = 0; l < KB; ++l) { Gm[k * KB + l] *= dn[k] * dn[l]; dev = fmax(dev, fabs(Gm[k * KB + l] - (k == l))); }
+      if (!(dev == dev)) { bax_set_error("rsx_calib_linear: non-finite subspace"); return BAX_E_NUMERIC; }
+      host_eigh(KB, Gm, w, U);
+      double cm[KB * KB + KB];
+      for (int k = 0; k < KB; ++k) for (int l = 0; l < KB; ++l) cm[k * KB + l] = dn[k] * U[k * KB + l] / sqrt(fmax(w[l], 1e-14 * w[KB - 1]));
+      for (int l = 0; l < KB; ++l) cm[KB * KB + l] = 0.0;
+      double dummy[KB];
+      if ((rc = mix(cm, false, dummy))) return rc;
+      mix_host(yt, cm);
+      if (dev < 1e-8 && pass > 0) break;
+      if (dev < 1e-13) break;
+    }
+    // W = H [Y; yt]
+    RSX_CU(cudaMemcpyAsync(d_tv.p, yt.data(), sizeof(double) * n3 * KB, cudaMemcpyHostToDevice, s));
+    k_arrow_point<<<nbp, 128, sm_pt, s>>>(2, C, Min, sigma, d_D.d(), d_Bt.d(), ldq, d_tv.d(), d_Y.d(), d_W.d());
+    RSX_CU(cudaGetLastError());
+    h->t_launch[RSX_T_FINAL] += 1;
+    if ((rc = bty(d_Y.d(), wt.data()))) return rc;
+    for (int a = 0; a < n3; ++a) for (int k = 0; k < KB; ++k) { double acc = wt[a * KB + k]; for (int b = 0; b < n3; ++b) acc += T[a * n3 + b] * yt[b * KB + k]; tmp[a * KB + k] = acc; }
+    wt = tmp;
+    if ((rc = gram(d_Y.d(), d_W.d(), red.data()))) return rc;
+    std::vector<double> Hm(KB * KB), w, Z;
+    for (int k = 0; k < KB; ++k) for (int l = 0; l < KB; ++l) { double a = red[KB * KB + k * KB + l]; for (int q = 0; q < n3; ++q) a += yt[q * KB + k] * wt[q * KB + l]; Hm[k * KB + l] = a; }
+    host_eigh(KB, Hm, w, Z);
+    double cm[KB * KB + KB], resx[KB];
+    for (int e = 0; e < KB * KB; ++e) cm[e] = Z[e];
+    for (int l = 0; l < KB; ++l) { cm[KB * KB + l] = w[l]; theta[l] = w[l]; }
+    if ((rc = mix(cm, true, resx))) return rc;
+    mix_host(yt, cm); mix_host(wt, cm);
+    double worst = 0;
+    for (int l = 0; l < 4; ++l) {
+      double r2 = resx[l];
+      for (int a = 0; a < n3; ++a) { const double r = wt[a * KB + l] - theta[l] * yt[a * KB + l]; r2 += r * r; }
+      worst = fmax(worst, sqrt(r2));
+    }
+    if (worst <= 1e-13 * scale) converged = 1;
+  }
+  if (info_host) { info_host[2] = it; info_host[3] = converged; }
+  // ---- 6. t_0 = 0 combination, scale, sign (calib_ransac.py:110-129)
+  double cf[4];
+  for (int j = 0; j < 4; ++j) {
+    double mnr[9]; int cc = 0;
+    for (int q = 0; q < 4; ++q) { if (q == j) continue; for (int r = 0; r < 3; ++r) mnr[3 * r + cc] = yt[r * KB + q]; ++cc; }
+    cf[j] = ((j & 1) ? -1.0 : 1.0) * det3(mnr);
+  }
+  std::vector<double> ut(n3);
+  for (int a = 0; a < n3; ++a) { ut[a] = 0; for (int j = 0; j < 4; ++j) ut[a] += yt[a * KB + j] * cf[j]; }
+  const double sc = sqrt(ut[3] * ut[3] + ut[4] * ut[4] + ut[5] * ut[5]);
+  double host_small[4 + 24];
+  for (int j = 0; j < 4; ++j) host_small[j] = cf[j] / sc;
+  for (int c = 0; c < 2; ++c) for (int r = 0; r < 3; ++r) { for (int j = 0; j < 3; ++j) host_small[4 + 12 * c + 4 * r + j] = Rh[9 * c + 3 * r + j]; host_small[4 + 12 * c + 4 * r + 3] = ut[3 * c + r] / sc; }
+  DevBuf d_small, d_Xtmp;
+  RSX_CU(d_small.alloc(sizeof(host_small) + 16, true, s));
+  RSX_CU(cudaMemcpyAsync(d_small.p, host_small, sizeof(host_small), cudaMemcpyHostToDevice, s));
+  unsigned long long* cnt = (unsigned long long*)h->red;
+  RSX_CU(cudaMemsetAsync(cnt, 0, 2 * sizeof(unsigned long long), s));
+  k_arrow_finish<<<nbp, 128, 0, s>>>(h->n, idx_m, M, Min, d_small.d() + 4, d_small.d(), d_Y.d(), X_out, cnt);
+  RSX_CU(cudaGetLastError());
+  unsigned long long hc[2];
+  RSX_CU(cudaMemcpyAsync(hc, cnt, sizeof(hc), cudaMemcpyDeviceToHost, s));
+  RSX_CU(cudaStreamSynchronize(s));
+  const double sign = hc[0] > hc[1] ? 1.0 : -1.0;
+  if (X_out && sign < 0) { k_scale_X<<<(unsigned)((Q + 255) / 256), 256, 0, s>>>(X_out, Q, -1.0); RSX_CU(cudaGetLastError()); }
+  std::vector<double> Rt(12 * C);
+  for (int c = 0; c < C; ++c) for (int r = 0; r < 3; ++r) { for (int j = 0; j < 3; ++j) Rt[12 * c + 4 * r + j] = Rh[9 * c + 3 * r + j]; Rt[12 * c + 4 * r + 3] = sign * ut[3 * c + r] / sc; }
+  RSX_CU(cudaMemcpyAsync(Rt_out, Rt.data(), sizeof(double) * 12 * C, cudaMemcpyHostToDevice, s));
+  RSX_CU(cudaStreamSynchronize(s));
+  h->t_launch[RSX_T_FINAL] += 2;
+  if (!converged) { bax_set_error("rsx_calib_linear: subspace iteration did not converge in %d iterations", max_it); return BAX_E_NUMERIC; }
+  return BAX_OK;
+}

@@ -1,0 +1,39 @@
+// rsx_handle: state of the RANSAC path (include/rsx.h), shared by rsx.cu and rsx_final.cu.
+#pragma once
+#include "bax_internal.cuh"
+#include "../../include/rsx.h"
+
+enum { RSX_T_FIT = 0, RSX_T_SCORE = 1, RSX_T_FINAL = 2, RSX_T_OTHER = 3, RSX_T_COUNT = 4 };
+
+struct rsx_handle {
+  int device, sm_count;
+  int C; int64_t N, M;
+  double* v;            // [C][N][3]  (copy)
+  double* n;            // [C][M][3]  (copy)
+  double* Rt;           // [cap_h][C][12] models of the current chunk
+  int64_t cap_h;
+  double* fit_scratch;  // global H/V workspace when 3(10+C) is too large for shared memory
+  size_t fit_scratch_bytes;
+  double* red;          // small reduction scratch
+  size_t red_bytes;
+  double* host_pinned;  // [64]
+  bax_handle* bx;       // borrowed SYRK / partial-sum machinery (only sm_count, syrk_part, partials, timing used)
+  int timing;
+  cudaEvent_t ev0, ev1;
+  double t_ms[RSX_T_COUNT];
+  int64_t t_launch[RSX_T_COUNT];
+};
+
+struct RsxTimer {
+  rsx_handle* h; int which; cudaStream_t s; int nl;
+  RsxTimer(rsx_handle* h_, int w, cudaStream_t s_, int launches) : h(h_), which(w), s(s_), nl(launches) {
+    if (h->timing) cudaEventRecord(h->ev0, s);
+  }
+  ~RsxTimer() {
+    h->t_launch[which] += nl;
+    if (h->timing) {
+      cudaEventRecord(h->ev1, s); cudaEventSynchronize(h->ev1);
+      float ms = 0; cudaEventElapsedTime(&ms, h->ev0, h->ev1); h->t_ms[which] += ms;
+    }
+  }
+};

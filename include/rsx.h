@@ -1,0 +1,74 @@
+/* rsx.h — C ABI of the B200-native RANSAC linear-calibration hot path (part of libbax.so).
+ *
+ * The reference (pure Python) has no FFI; its boundary for this path is the set of Python functions
+ * in calib_ransac.py.  Each entry point names the reference lines it replaces.  Unless marked "host",
+ * array arguments are CUDA DEVICE pointers; calls are ordered on the given cudaStream_t (void*; 0 =
+ * legacy default stream) and return 0 or a negative BAX_E_* code (bax_last_error() has the text).
+ *
+ *   v [C][N][3]  unit bone directions per camera        (calib_ransac.py:243, util.py:496-544)
+ *   n [C][M][3]  K^-1-normalised rays [u, v, 1]         (calib_ransac.py:256-270)
+ *   a hypothesis = 10 direction indices + 10 ray indices (calib_ransac.py:150-151)
+ */
+#ifndef RSX_H
+#define RSX_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RSX_SAMPLE 10   /* minimal-sample size hard-coded at calib_ransac.py:150-151 */
+
+typedef struct rsx_handle rsx_handle;
+
+int rsx_create(int device, rsx_handle** out);
+int rsx_destroy(rsx_handle* h);
+
+/* HOST ONLY, no GPU needed.  The reference's sequential sample stream (calib_ransac.py:148-151):
+ * rng = np.random.default_rng(seed); per hypothesis rng.choice(N, 10, replace=False) then
+ * rng.choice(M, 10, replace=False).  NumPy's algorithm restated: PCG64 (XSL-RR 128/64) with its 32-bit
+ * half-word buffer, Lemire bounded integers, Floyd's sampling and the trailing Fisher-Yates shuffle.
+ * pcg[0..5] = { state_hi, state_lo, inc_hi, inc_lo, has_uint32, uinteger } as read from
+ * Generator.bit_generator.state; updated in place so a stream can be continued in chunks.
+ * samp_v, samp_m: host int32 [H][10]. */
+int rsx_sample_stream(uint64_t* pcg, int64_t N, int64_t M, int64_t H, int32_t* samp_v, int32_t* samp_m);
+
+/* Bind the scene: copies v and n into the handle's structure-of-arrays layout. */
+int rsx_problem_set(rsx_handle* h, int C, int64_t N, int64_t M, const double* v, const double* n, void* stream);
+
+/* calib_linear on each minimal sample (calib_ransac.py:51-131 called at :152) and its continuous score
+ * (calib_ransac.py:154-180):  score = ||reprojection error||_2 / M + ||angular error||_2 / N.
+ *   samp_v, samp_m  device int32 [H][10]
+ *   score           device [H]
+ *   Rt              device [H][C][12] (row-major [R | t] per camera) or NULL
+ *   parts           device [H][2] = { sum e^2, sum e3d^2 } or NULL */
+int rsx_fit_score(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, int64_t H, double* score,
+                  double* Rt, double* parts, void* stream);
+
+/* First minimum of score[0..H) (strict '<' from +inf: NaN and +inf never win, calib_ransac.py:182).
+ * best_host[0] = index or -1, score_host[0] = its score. Synchronises. */
+int rsx_argmin(rsx_handle* h, const double* score, int64_t H, int64_t* best_host, double* score_host, void* stream);
+
+/* Inlier masks of one model (calib_ransac.py:193-204):  mask2d[i] = all_c K00[c] * ||e_ci[:2]|| <= th2d,
+ * mask3d[i] = e3d_i <= th3d.   Rt device [C][12]; K00 device [C]; mask2d uint8 [M], mask3d uint8 [N];
+ * e_out [M][C][3] and e3d_out [N] optional (NULL).  counts_host[0..1] = inliers 2-D, 3-D. Synchronises. */
+int rsx_winner_masks(rsx_handle* h, const double* Rt, const double* K00, double th2d, double th3d,
+                     uint8_t* mask2d, uint8_t* mask3d, double* e_out, double* e3d_out, int64_t* counts_host,
+                     void* stream);
+
+/* calib_linear (calib_ransac.py:51-131) on the subsets selected by the masks (NULL = all): the final
+ * inlier fit at calib_ransac.py:209 and, with NULL masks, calib_linear.py's one-shot model fit.
+ * The 3(M_in + C) eigenproblem is never densified: rotations from the 3C x 3C Gram matrix; translations
+ * from the 6 smallest eigenpairs of the arrow-structured normal matrix by block-eliminated inverse subspace
+ * iteration with Rayleigh-Ritz.  Rt_out device [C][12]; X_out device [M_in][3] or NULL;
+ * info_host[0..3] = { M_in, N_in, iterations, converged }. Synchronises. */
+int rsx_calib_linear(rsx_handle* h, const uint8_t* mask3d, const uint8_t* mask2d, double* Rt_out, double* X_out,
+                     int64_t* info_host, void* stream);
+
+/* timing hooks: CUDA-event ms and launch counts of { fit, score, final } since the last reset */
+int rsx_timing_enable(rsx_handle* h, int on);
+int rsx_timing_read(rsx_handle* h, double* ms_host /*[4]*/, int64_t* launches_host /*[4]*/);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,38 @@
+// TEST INFRASTRUCTURE ONLY: runs the __host__ __device__ numerics of csrc/rsx_*.cuh on the CPU (one "thread",
+// syncs are no-ops) so the `-m "not gpu"` tests can check the device math against the oracle without a GPU.
+// Never linked into libbax.so, never imported by the package.
+#include "../../extrinsic-camera-calibration-from-a-moving-person_b200/csrc/rsx_fit.cuh"
+#include <stdlib.h>
+#include <vector>
+
+extern "C" int emu_jacobi(int n, double* A /*[n][n] in, diag out*/, double* V /*[n][n]*/) {
+  const int ld = n | 1;
+  std::vector<double> a((size_t)n * ld), v((size_t)n * ld), cs(2 * (n / 2 + 1));
+  int flag[2];
+  for (int i = 0; i < n; ++i) for (int j = 0; j < n; ++j) a[i * ld + j] = A[i * n + j];
+  CtaCtx g{0, 1};
+  int sweeps = cta_jacobi(g, a.data(), v.data(), n, ld, cs.data(), flag, 60);
+  for (int i = 0; i < n; ++i) for (int j = 0; j < n; ++j) { A[i * n + j] = a[i * ld + j]; V[i * n + j] = v[i * ld + j]; }
+  return sweeps;
+}
+extern "C" void emu_eig4(const double* A16, double* x4) {
+  double a[4][4], x[4];
+  for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) a[i][j] = A16[4 * i + j];
+  eig4_smallest(a, x);
+  for (int i = 0; i < 4; ++i) x4[i] = x[i];
+}
+extern "C" void emu_fit(int C, long long N, long long M, const double* v, const double* n, const int* sv, const int* sm,
+                        double* Rt_out) {
+  const int nu = 3 * (RSX_S + C), ld = nu | 1;
+  std::vector<double> buf(fit_ws_small_doubles(C) + 2 * (size_t)nu * ld);
+  FitWs ws; fit_ws_carve(buf.data(), nullptr, C, ws);
+  CtaCtx g{0, 1};
+  fit_hypothesis(g, C, N, M, v, n, sv, sm, ws, Rt_out);
+}
+extern "C" void emu_score(int C, long long N, long long M, const double* v, const double* n, const double* Rt,
+                          double* parts2, double* e_out, double* e3d_out, const double* K00, double th2d, double th3d,
+                          unsigned char* mask2d, unsigned char* mask3d) {
+  CtaCtx g{0, 1};
+  parts2[0] = score_points(g, C, M, n, Rt, e_out, K00, th2d, mask2d);
+  parts2[1] = score_dirs(g, C, N, v, Rt, e3d_out, th3d, mask3d);
+}

@@ -1,0 +1,151 @@
+"""CPU-only checks: the C-ABI library loads and exports every symbol declared in include/*.h; the NumPy-compatible
+sample stream (host C++); and the device numerics of the RANSAC path run through the host emulation build
+(tests/hostemu, same __host__ __device__ code as the kernels) against golden vectors of the unmodified reference."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+import calib_b200  # noqa: F401
+from calib_b200 import _lib, _rsx_sigs
+from oracle import ransac_oracle as ro
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+P = C.POINTER(C.c_double)
+
+
+def dp(a):
+    return a.ctypes.data_as(P)
+
+
+def _declared(header):
+    txt = open(os.path.join(ROOT, "include", header)).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b((?:bax|rsx)_[a-z0-9_]+)\s*\(", txt)))
+
+
+@pytest.mark.parametrize("header", ["bax.h", "rsx.h"])
+def test_library_exports_every_declared_symbol(header):
+    L = _lib.lib()
+    names = _declared(header)
+    assert len(names) >= 8
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/{header} but not exported by libbax.so"
+    bound = set(_lib.exported_symbols()) | set(_rsx_sigs.exported_symbols())
+    assert set(names) <= bound, f"ctypes binding missing for {set(names) - bound}"
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from calib_b200 import ba, calib_ransac
+    with pytest.raises(_lib.BaxError):
+        ba.BAProblem(np.eye(3)[None], np.zeros((1, 1, 1, 2)), np.ones((1, 1, 1)), None, None)
+    with pytest.raises(_lib.BaxError):
+        calib_ransac.RansacProblem(np.zeros((2, 10, 3)), np.zeros((2, 10, 3)))
+
+
+@pytest.mark.parametrize("N,M,H,seed", [(360, 750, 400, 0), (12000, 15000, 300, 7), (10, 10, 50, 1), (11, 4000, 64, 123)])
+def test_sample_stream_matches_numpy(N, M, H, seed):
+    from calib_b200 import calib_ransac as cr
+    sn, sm = cr.sample_indices(N, M, H, seed)
+    rn, rm = ro.sample_indices(N, M, H, seed)          # np.random.default_rng(seed).choice(...), calib_ransac.py:148-151
+    assert np.array_equal(sn, rn) and np.array_equal(sm, rm)
+
+
+@pytest.mark.parametrize("case", ["c4", "c3"])
+def test_sample_stream_matches_reference_golden(golden_dir, case):
+    from calib_b200 import calib_ransac as cr
+    g = np.load(os.path.join(golden_dir, f"ransac_{case}.npz"))
+    sn, sm = cr.sample_indices(g["vc"].shape[1], g["n"].shape[1], int(g["n_iter"]), int(g["seed"]))
+    assert np.array_equal(sn, g["sn"]) and np.array_equal(sm, g["sm"])
+
+
+def test_ransac_inputs_match_reference_golden(golden_dir):
+    from calib_b200 import calib_ransac as cr
+    from calib_b200.ba import OP_BONE
+    for case in ("c4", "c3"):
+        g = np.load(os.path.join(golden_dir, f"ransac_{case}.npz"))
+        v, n = cr.ransac_inputs(g["p3d"], g["s3d"], g["p2d"], g["s2d"], g["K"], OP_BONE)
+        assert np.array_equal(v, g["vc"]) and np.array_equal(n, g["n"])
+
+
+def test_shard_ranges_cover_all_hypotheses():
+    from calib_b200 import calib_ransac as cr
+    for n_iter in (1, 7, 100000):
+        for world in (1, 2, 3, 8):
+            r = [cr.shard_range(n_iter, k, world) for k in range(world)]
+            assert r[0][0] == 0 and r[-1][1] == n_iter
+            assert all(r[k][1] == r[k + 1][0] for k in range(world - 1))
+
+
+# ---------------------------------------------------------------- device math through the host emulation
+@pytest.fixture(scope="module")
+def emu():
+    so = os.path.join(ROOT, "tests", "hostemu", "librsx_hostemu.so")
+    src = os.path.join(ROOT, "tests", "hostemu", "rsx_hostemu.cu")
+    if not os.path.isfile(so):
+        subprocess.check_call(["bash", os.path.join(ROOT, "tests", "hostemu", "build.sh")])
+    assert os.path.isfile(so) and os.path.isfile(src)
+    return C.CDLL(so)
+
+
+@pytest.mark.parametrize("n", [4, 10, 41, 42])
+def test_emulated_cta_jacobi(emu, n):
+    rng = np.random.default_rng(n)
+    B = rng.normal(size=(n + 5 if n != 42 else 30, n))
+    A0 = B.T @ B
+    A, V = A0.copy(), np.zeros((n, n))
+    sweeps = emu.emu_jacobi(n, dp(A), dp(V))
+    assert sweeps < 40
+    w = np.diag(A).copy()
+    assert np.linalg.norm(V.T @ V - np.eye(n)) < 1e-12
+    assert np.linalg.norm(A0 @ V - V * w) <= 1e-13 * np.linalg.norm(A0)
+    assert np.max(np.abs(np.sort(w) - np.linalg.eigvalsh(A0))) <= 1e-13 * np.max(w)
+
+
+def test_emulated_eig4(emu):
+    rng = np.random.default_rng(0)
+    for _ in range(200):
+        B = rng.normal(size=(rng.integers(3, 9), 4))
+        A = B.T @ B
+        x = np.zeros(4)
+        emu.emu_eig4(dp(np.ascontiguousarray(A)), dp(x))
+        w, v = np.linalg.eigh(A)
+        assert abs(abs(x @ v[:, 0]) - 1) < 1e-9 or w[1] - w[0] < 1e-6 * w[3]
+        assert abs(x @ A @ x - w[0]) <= 1e-12 * w[3]
+
+
+@pytest.mark.parametrize("case", ["c4", "c3"])
+def test_emulated_fit_score_masks_vs_reference_golden(emu, golden_dir, case):
+    g = np.load(os.path.join(golden_dir, f"ransac_{case}.npz"))
+    v, n = np.ascontiguousarray(g["vc"]), np.ascontiguousarray(g["n"])
+    Cn, N, M = v.shape[0], v.shape[1], n.shape[1]
+    pi = C.POINTER(C.c_int)
+    models = []
+    for h in range(int(g["n_iter"])):
+        sv = np.ascontiguousarray(g["sn"][h], dtype=np.int32)
+        sm = np.ascontiguousarray(g["sm"][h], dtype=np.int32)
+        Rt = np.zeros((Cn, 3, 4))
+        emu.emu_fit(Cn, C.c_longlong(N), C.c_longlong(M), dp(v), dp(n), sv.ctypes.data_as(pi), sm.ctypes.data_as(pi), dp(Rt))
+        assert np.max(np.abs(Rt[:, :, :3] - g["R_hyp"][h])) < 1e-9
+        assert np.max(np.abs(Rt[:, :, 3:] - g["t_hyp"][h])) < 1e-9
+        parts = np.zeros(2)
+        emu.emu_score(Cn, C.c_longlong(N), C.c_longlong(M), dp(v), dp(n), dp(Rt), dp(parts), None, None, None,
+                      C.c_double(0), C.c_double(0), None, None)
+        score = np.sqrt(parts[0]) / M + np.sqrt(parts[1]) / N
+        assert abs(score - g["scores"][h]) <= 1e-9 * g["scores"][h]
+        models.append((score, Rt))
+    best = int(np.argmin([m[0] for m in models]))
+    assert best == int(g["best"])
+    m2, m3 = np.zeros(M, np.uint8), np.zeros(N, np.uint8)
+    K00 = np.ascontiguousarray(g["K"][:, 0, 0])
+    pu = C.POINTER(C.c_ubyte)
+    parts = np.zeros(2)
+    emu.emu_score(Cn, C.c_longlong(N), C.c_longlong(M), dp(v), dp(n), dp(models[best][1]), dp(parts), None, None, dp(K00),
+                  C.c_double(float(g["th_2d"])), C.c_double(float(g["th_3d"])), m2.ctypes.data_as(pu), m3.ctypes.data_as(pu))
+    assert np.array_equal(m2.astype(bool), g["mask_2d"]) and np.array_equal(m3.astype(bool), g["mask_3d"])
