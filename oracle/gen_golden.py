@@ -142,8 +142,34 @@ def gen_ransac(name, scene_kw, n_iter, seed, th_2d, th_3d_deg):
           "inliers", mask_2d.sum(), mask_3d.sum())
 
 
-if __name__ == "__main__":
+def gen_cli(name="cli_c4"):
+    """File-level golden: a tiny scene written in the reference's directory layout by dataio.write_scene, read back
+    by the reference's own util.load_eldersim and pushed through its main_ransac (calib_ransac.py:212-277)."""
+    import tempfile
+    dataio = importlib.import_module("extrinsic-camera-calibration-from-a-moving-person_b200.dataio")
+    _, rc, ru = ref_shim.load()
+    kw = dict(C=4, N=24, seed=31, p_drop_2d=0.1, p_drop_3d=0.05)
+    sc = scene_mod.make_scene(**kw)
+    aid, pid, gid, frame_skip, n_iter, seed = 23, 102, 3, 2, 5, 0
+    with tempfile.TemporaryDirectory() as tmp:
+        d = os.path.join(tmp, "noise_3_0")
+        dataio.write_scene(d, sc, aid, pid, gid)
+        loaded = ru.load_eldersim(d, gid, aid, pid)
+        with quiet(), contextlib.redirect_stderr(io.StringIO()):
+            R, t, _, _, camid, K = rc.main_ransac(d, gid, aid, pid, ru.OP_BONE, ru.OP_KEY_SUB, frame_skip=frame_skip,
+                                                  n_iter=n_iter, th_2d=50.0, th_3d=5.0 / 180 * np.pi, seed=seed)
+    np.savez_compressed(os.path.join(OUT, f"{name}.npz"), scene_kw=str(kw), aid=aid, pid=pid, gid=gid,
+                        frame_skip=frame_skip, n_iter=n_iter, seed=seed, R_ransac=R, t_ransac=t, CAMID=camid, K=K,
+                        p3d=loaded[5], s3d=loaded[6], p2d=loaded[7], s2d=loaded[8], frames=loaded[9],
+                        versions=str(versions()))
+    print("wrote", name)
+
+
+def main():
     os.makedirs(OUT, exist_ok=True)
+    if len(sys.argv) > 1 and sys.argv[1] == "cli":
+        gen_cli()
+        return
     gen_ba("small", dict(C=4, N=6, seed=11), list(range(17)), 1.0, 1.0, run_main=True)
     gen_ba("partial", dict(C=5, N=8, seed=12, score_mode="uniform", p_drop_2d=0.3, p_drop_3d=0.1),
            list(range(17)), 3.0, 7.0)
@@ -152,3 +178,8 @@ if __name__ == "__main__":
     gen_ba("gafa_lambda", dict(C=3, N=7, seed=14, score_mode="uniform"), list(range(17)), 1.0, 1e5)
     gen_ransac("c4", dict(C=4, N=40, seed=21, p_drop_2d=0.1, p_drop_3d=0.05), 12, 0, 50.0, 5.0)
     gen_ransac("c3", dict(C=3, N=30, seed=22, sigma_px=1.0), 8, 7, 50.0, 5.0)
+    gen_cli()
+
+
+if __name__ == "__main__":
+    main()
