@@ -73,6 +73,7 @@ struct bax_handle {
   size_t partials_bytes;
   double* host_pinned;       // small pinned staging for scalars
   // ---- timing
+  int rj_variant;            // tuning knob (env BAX_RJ_VARIANT): 0 = per-warp staged LSU stores; 1/2/3 = CTA-staged TMA bulk stores (256x4, 128x8 [default], 256x3)
   int timing;
   cudaEvent_t ev0, ev1;
   double t_ms[BAX_T_COUNT];

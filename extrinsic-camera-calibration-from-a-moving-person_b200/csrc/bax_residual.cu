@@ -89,6 +89,113 @@ k_rj(const double* __restrict__ campack, const double* __restrict__ x, const dou
   for (int i = lane; i < 3 * nw; i += 32) jq[i] = stage[warp][(i / 3) * 9 + 6 + (i % 3)];
 }
 
+// Bulk-store variant: the whole CTA stages its compacted rows in shared memory in their final global layout
+// (the rows of one CTA are contiguous in r2 / Jcam / Jpt), then three elected threads hand the three runs to the
+// TMA engine (cp.async.bulk shared::cta -> global).  The LSU issues no global stores for the Jacobian blocks, the
+// register budget drops (values go to shared memory as soon as they exist) and NT*MINB threads stay resident.
+__device__ __forceinline__ void bulk_store_s2g(void* gdst, const void* ssrc, unsigned bytes) {
+  unsigned sa = (unsigned)__cvta_generic_to_shared(ssrc);
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n" ::"l"(gdst), "r"(sa), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;\n" ::: "memory");
+  asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");
+}
+
+template <int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB)
+k_rj_bulk(const double* __restrict__ campack, const double* __restrict__ x, const double2* __restrict__ y,
+          const double* __restrict__ s, int64_t P, const int64_t* __restrict__ blockbase, int sub /*CTAs per 256-block*/,
+          double2* __restrict__ r2, double2* __restrict__ Jcam, double2* __restrict__ Jpt,
+          int32_t* __restrict__ obs_cam, int32_t* __restrict__ obs_pt) {
+  extern __shared__ __align__(128) unsigned char smraw[];
+  double2* stJc = reinterpret_cast<double2*>(smraw);          // [NT][6]
+  double2* stJp = stJc + NT * 6;                              // [NT][3]
+  double2* stR = stJp + NT * 3;                               // [NT]
+  __shared__ double cam[CAMPACK];
+  __shared__ int s_warp[NT / 32];
+  const int c = blockIdx.y;
+  if (threadIdx.x < CAMPACK) cam[threadIdx.x] = campack[(size_t)c * CAMPACK + threadIdx.x];
+  // blockbase is per 256 observations; a CTA of NT < 256 threads covers a 1/sub slice of one such block
+  const int blk256 = blockIdx.x / sub, part = blockIdx.x - blk256 * sub;
+  const int64_t p0 = (int64_t)blk256 * 256;
+  const int64_t p = p0 + part * NT + threadIdx.x;
+  double sc = 0.0; double2 yy = make_double2(0, 0);
+  if (p < P) { sc = s[(size_t)c * P + p]; yy = y[(size_t)c * P + p]; }
+  const bool vis = sc > 0;
+  const unsigned bal = __ballot_sync(0xffffffffu, vis);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int wr = __popc(bal & ((1u << lane) - 1u));
+  if (lane == 0) s_warp[warp] = __popc(bal);
+  // visible observations of the earlier slices of this 256-block (sub > 1 only)
+  int before = 0;
+  if (sub > 1) {
+    for (int q = 0; q < part; ++q) {
+      int cnt = 0;
+      for (int i = lane; i < NT; i += 32) { int64_t pp = p0 + q * NT + i; cnt += (pp < P && s[(size_t)c * P + pp] > 0) ? 1 : 0; }
+      for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+      before += cnt;
+    }
+  }
+  __syncthreads();
+  int wbase = 0, ntot = 0;
+#pragma unroll
+  for (int w = 0; w < NT / 32; ++w) { const int v = s_warp[w]; wbase += (w < warp) ? v : 0; ntot += v; }
+  const int64_t row0 = blockbase[(size_t)c * (gridDim.x / sub) + blk256] + before;   // first row of this CTA
+  if (vis) {
+    const int rk = wbase + wr;
+    if (obs_cam) { obs_cam[row0 + rk] = c; obs_pt[row0 + rk] = (int32_t)p; }
+    // same arithmetic as obs_linearize<true>, ordered so that every block is parked in shared memory as soon as
+    // it exists (keeps the live set near 18 doubles)
+    const double* K = cam; const double* R = cam + 9; const double* t = cam + 18; const double* M = cam + 21;
+    const double x0 = x[3 * p], x1 = x[3 * p + 1], x2 = x[3 * p + 2];
+    double jt[2][3];
+    {
+      const double P0 = R[0] * x0 + R[1] * x1 + R[2] * x2 + t[0];
+      const double P1 = R[3] * x0 + R[4] * x1 + R[5] * x2 + t[1];
+      const double P2 = R[6] * x0 + R[7] * x1 + R[8] * x2 + t[2];
+      const double q0 = K[0] * P0 + K[1] * P1 + K[2] * P2;
+      const double q1 = K[3] * P0 + K[4] * P1 + K[5] * P2;
+      const double q2 = K[6] * P0 + K[7] * P1 + K[8] * P2;
+      const double w = 1.4142135623730951 * sc;
+      const double yh0 = q0 / q2, yh1 = q1 / q2;
+      stR[rk] = make_double2((yy.x - yh0) * w, (yy.y - yh1) * w);
+      const double f = -w / q2;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        jt[0][k] = f * (K[k] - yh0 * K[6 + k]);
+        jt[1][k] = f * (K[3 + k] - yh1 * K[6 + k]);
+      }
+    }
+    double jp[2][3];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int k = 0; k < 3; ++k) jp[a][k] = jt[a][0] * R[k] + jt[a][1] * R[3 + k] + jt[a][2] * R[6 + k];
+    double2* b = stJp + rk * 3;
+    b[0] = make_double2(jp[0][0], jp[0][1]);
+    b[1] = make_double2(jp[0][2], jp[1][0]);
+    b[2] = make_double2(jp[1][1], jp[1][2]);
+    double2* aout = stJc + rk * 6;
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+      const double c0 = x1 * jp[a][2] - x2 * jp[a][1];
+      const double c1 = x2 * jp[a][0] - x0 * jp[a][2];
+      const double c2 = x0 * jp[a][1] - x1 * jp[a][0];
+      const double r0 = c0 * M[0] + c1 * M[3] + c2 * M[6];
+      const double r1 = c0 * M[1] + c1 * M[4] + c2 * M[7];
+      const double r2v = c0 * M[2] + c1 * M[5] + c2 * M[8];
+      aout[3 * a + 0] = make_double2(r0, r1);
+      aout[3 * a + 1] = make_double2(r2v, jt[a][0]);
+      aout[3 * a + 2] = make_double2(jt[a][1], jt[a][2]);
+    }
+    asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");   // generic-proxy writes -> visible to the async proxy
+  }
+  __syncthreads();
+  if (ntot == 0) return;
+  if (threadIdx.x == 0) bulk_store_s2g(Jcam + row0 * 6, stJc, (unsigned)ntot * 96u);
+  else if (threadIdx.x == 32) bulk_store_s2g(Jpt + row0 * 3, stJp, (unsigned)ntot * 48u);
+  else if (threadIdx.x == 64) bulk_store_s2g(r2 + row0, stR, (unsigned)ntot * 16u);
+}
+
 // ------------------------------------------------------------------ orientation rows  (ba.py:67-96)
 __global__ void k_var3d_residual(const double* __restrict__ campack, const double* __restrict__ dhat,
                                  int C, int64_t Nv, double lam1, double* __restrict__ r_out) {
@@ -208,9 +315,35 @@ extern "C" int bax_residual_jacobian(bax_handle* h, const double* theta, double*
   int rc = bax_launch_cam_prep(h, theta, s); if (rc) return rc;
   {
     BaxTimer t(h, BAX_T_RJ, s, 1);
-    k_rj<<<dim3(h->nblk_obs, h->C), 256, 0, s>>>(h->campack, theta + 6 * h->C, (const double2*)h->y2d, h->s2d,
-                                                 h->P, h->blockbase, (double2*)r2, (double2*)Jcam, (double2*)Jpt,
-                                                 obs_cam, obs_pt);
+    const double* x = theta + 6 * h->C;
+#define RJ_ARGS h->campack, x, (const double2*)h->y2d, h->s2d, h->P, h->blockbase
+#define RJ_OUT (double2*)r2, (double2*)Jcam, (double2*)Jpt, obs_cam, obs_pt
+    switch (h->rj_variant) {
+      case 0:
+        k_rj<<<dim3(h->nblk_obs, h->C), 256, 0, s>>>(RJ_ARGS, RJ_OUT);
+        break;
+      case 2: {
+        const int smem = 128 * 160;
+        k_rj_bulk<128, 8><<<dim3(h->nblk_obs * 2, h->C), 128, smem, s>>>(RJ_ARGS, 2, RJ_OUT);
+        break;
+      }
+      case 3: {
+        const int smem = 256 * 160;
+        static bool once = false;
+        if (!once) { BAX_CUDA(cudaFuncSetAttribute(k_rj_bulk<256, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); once = true; }
+        k_rj_bulk<256, 3><<<dim3(h->nblk_obs, h->C), 256, smem, s>>>(RJ_ARGS, 1, RJ_OUT);
+        break;
+      }
+      default: {
+        const int smem = 256 * 160;
+        static bool once = false;
+        if (!once) { BAX_CUDA(cudaFuncSetAttribute(k_rj_bulk<256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); once = true; }
+        k_rj_bulk<256, 4><<<dim3(h->nblk_obs, h->C), 256, smem, s>>>(RJ_ARGS, 1, RJ_OUT);
+        break;
+      }
+    }
+#undef RJ_ARGS
+#undef RJ_OUT
   }
   BAX_LAUNCH_CHECK();
   return BAX_OK;
