@@ -187,53 +187,82 @@ def run_gpu(args):
         return v
 
     # ---------------- device-resident LM iterations
-    sol = ba.TRFSolver(prob, theta0, ftol=0.0, xtol=0.0, gtol=0.0)
+    class Runner:
+        """LM iterations of complete solves: iterate from theta0 with the reference's own tolerances (ftol 1e-4,
+        xtol 1e-8, gtol 1e-8: ba.py:187-206) and, when SciPy's termination test fires, start the next solve from
+        theta0 — so the timed steps are the iteration mix of real runs (first iterations included), not iterations
+        at a stationary point.  The restart's own linearisation is inside the timed region."""
+
+        def __init__(self):
+            self.nfev, self.restarts = 0, 0
+            self.sol = ba.TRFSolver(prob, theta0)
+
+        def iterate(self):
+            self.sol.iterate()
+            if self.sol.done():
+                self.nfev += self.sol.nfev
+                self.restarts += 1
+                self.sol = ba.TRFSolver(prob, theta0)
+
+        def counts(self):
+            return (self.nfev + self.sol.nfev, prob.n_trials)
+
+    run = Runner()
     for _ in range(args.warmup):
-        sol.iterate()
+        run.iterate()
     launches0 = sum(v[1] for v in prob.timing_read().values())
-    nfev0, trials0 = sol.nfev, sum(h["n_it"] + 1 for h in sol.history)
+    nfev0, trials0 = run.counts()
     sampler = ClockSampler(local_rank)
     sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record()
     for _ in range(args.steps):
-        sol.iterate()
+        run.iterate()
     ev1.record()
     barrier()
     ms_total = max_over_ranks(ev0.elapsed_time(ev1))
     sampler.stop_flag = True
     launches = sum(v[1] for v in prob.timing_read().values()) - launches0
-    nfev = sol.nfev - nfev0
-    trials = sum(h["n_it"] + 1 for h in sol.history) - trials0
+    nfev1, trials1 = run.counts()
+    nfev, trials = nfev1 - nfev0, trials1 - trials0
+    sol = run.sol
     value = n_obs * args.steps / (ms_total * 1e-3)
 
     # ---------------- end to end: host buffers in, host result out, every step
-    Delta, alpha = sol.Delta, sol.alpha
-    theta_h.copy_(sol.x)
+    lm_cost = sol.cost
+    theta0_h = torch.from_numpy(theta0.copy()).pin_memory()
+    st8 = {"Delta": None, "alpha": 0.0}
+    theta_h.copy_(theta0_h)
     torch.cuda.synchronize()
     x_dev = torch.empty_like(sol.x)
-    cost_h = torch.zeros(1, dtype=torch.float64).pin_memory()
 
     def e2e_step():
         prob.y.copy_(y_h, non_blocking=True)
         prob.s.copy_(s_h, non_blocking=True)
         x_dev.copy_(theta_h, non_blocking=True)
-        s2 = ba.TRFSolver(prob, x_dev, ftol=0.0, xtol=0.0, gtol=0.0)
-        s2.Delta, s2.alpha = Delta, alpha
+        s2 = ba.TRFSolver(prob, x_dev)                 # linearises at the uploaded theta
+        if st8["Delta"] is not None:
+            s2.Delta, s2.alpha = st8["Delta"], st8["alpha"]
         s2.iterate(relinearize=False)
-        theta_h.copy_(s2.x, non_blocking=True)
+        if s2.status is None:
+            theta_h.copy_(s2.x, non_blocking=True)
+            st8["Delta"], st8["alpha"] = s2.Delta, s2.alpha
+        else:                                          # solve finished: the next step starts a new one
+            theta_h.copy_(s2.x, non_blocking=True)
+            torch.cuda.synchronize()
+            theta_h.copy_(theta0_h)
+            st8["Delta"], st8["alpha"] = None, 0.0
         torch.cuda.synchronize()
         return s2
 
     for _ in range(min(args.warmup, 2)):
         e2e_step()
-    k_e2e = max(1, min(args.steps, 5))
+    k_e2e = max(1, args.steps)
     barrier()
     t0 = time.perf_counter()
     for _ in range(k_e2e):
-        s2 = e2e_step()
-        Delta, alpha = s2.Delta, s2.alpha
+        e2e_step()
     torch.cuda.synchronize()
     t_e2e = max_over_ranks(time.perf_counter() - t0)
     e2e_value = n_obs * k_e2e / t_e2e
@@ -269,6 +298,7 @@ def run_gpu(args):
             roofline["traffic"] = tr.get("dram_bytes_per_launch")
 
     # ---------------- kernel shares of one LM iteration (separate instrumented pass; events add syncs)
+    sol = ba.TRFSolver(prob, theta0, ftol=0.0, xtol=0.0, gtol=0.0)
     prob.timing(True)
     for _ in range(2):
         sol.iterate()
@@ -292,11 +322,11 @@ def run_gpu(args):
                            "cache": "inputs larger than L2 (observations + whitened blocks >> 126 MB)",
                            "parallelism": f"frames sharded over {world} GPU(s); all-reduce of the packed camera blocks"},
                 "lm": {"cost_evaluations_per_step": nfev / args.steps, "damped_solves_per_step": trials / args.steps,
-                       "cost": sol.cost, "kernel_ms_2_steps": shares},
+                       "cost": lm_cost, "restarts": run.restarts, "kernel_ms_2_steps": shares},
                 "e2e": {"value": e2e_value, "unit": "observations/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "steps": k_e2e, "ms_per_step": t_e2e / k_e2e * 1e3,
                         "note": "every step: pinned-host observations + theta -> device, one full LM iteration "
-                                "(linearise, solves, cost evaluations), theta -> host"},
+                                "(linearise, solves, cost evaluations), theta -> host; same solve-restart rule as value"},
                 "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
                 "clocks": sampler.summary()}
     # ---------------- RANSAC leg (hypotheses/s), BASELINE configs[1]

@@ -132,6 +132,7 @@ class BAProblem:
             check(self.L.bax_set_global_frames(self.h, int(n_frames_global)), "bax_set_global_frames")
         self._out4 = (C.c_double * 8)()
         self.h_scale = 0.0
+        self.n_trials = 0                     # damped solves so far (bench accounting)
 
     def close(self):
         if getattr(self, "h", None):
@@ -270,6 +271,7 @@ class BAProblem:
         """Solve (J^T J + alpha I) p = -g; p lands in self.step (device).
         -> (||p||^2, g.p, p^T (J^T J + alpha I)^-1 p)."""
         st = _stream()
+        self.n_trials += 1
         with torch.cuda.device(self.dev):
             check(self.L.bax_trial_begin(self.h, float(alpha), st), "bax_trial_begin")
             self._allreduce(_lib.BUF_SCHUR)
@@ -325,6 +327,11 @@ def _solve_tr(prob, Delta, g_norm2, initial_alpha, rtol=0.01, max_iter=10):
         return max(0.001 * alpha_upper, (alpha_lower * alpha_upper) ** 0.5, alpha_floor)
 
     if initial_alpha is None or initial_alpha == 0:
+        # first solve of a run: Delta_0 = ||x_0|| is far larger than any sensible step, so probe the floor first —
+        # if that (Gauss-Newton-like) step is interior, the loop below would only walk alpha down to it
+        pn2, gp, _ = prob.trial(alpha_floor, False)
+        if math.sqrt(pn2) <= Delta:
+            return alpha_floor, 0, math.sqrt(pn2), gp, False
         alpha = reset()
     else:
         alpha = max(initial_alpha, alpha_floor)
@@ -338,6 +345,8 @@ def _solve_tr(prob, Delta, g_norm2, initial_alpha, rtol=0.01, max_iter=10):
         phi = p_norm - Delta
         if phi < 0 and alpha <= alpha_floor:
             return alpha, it + 1, p_norm, gp, False          # interior (Gauss-Newton-like) step
+        if not (ptq > 0 and p_norm > 0):
+            break                                             # step underflowed (start is already stationary)
         phi_prime = -ptq / p_norm
         if phi < 0:
             alpha_upper = alpha

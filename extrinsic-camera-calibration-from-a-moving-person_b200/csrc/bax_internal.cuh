@@ -207,6 +207,8 @@ __device__ __forceinline__ void chol3_bwd(const Chol3& c, double& a, double& b, 
 int bax_launch_cam_prep(bax_handle* h, const double* theta, cudaStream_t s, bool lin = false);
 int bax_syrk(bax_handle* h, const double* X, int rows, int64_t K, int64_t ldx, double* out /*[rows][rows]*/,
              cudaStream_t s);
+int bax_syrk_aug(bax_handle* h, const double* X, int rows, int ne, int64_t K, int64_t ldx, double* out /*[rows+ne][ldo]*/, int ldo,
+                 cudaStream_t s);
 int bax_dense_solve1(bax_handle* h, cudaStream_t s);
 int bax_dense_solve2(bax_handle* h, cudaStream_t s);
 int bax_scatter_cam_step(bax_handle* h, double* step, cudaStream_t s);

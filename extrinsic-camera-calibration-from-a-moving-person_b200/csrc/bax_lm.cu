@@ -358,7 +358,7 @@ extern "C" int bax_linearize_mid(bax_handle* h, void* stream) {
       BAX_LAUNCH_CHECK();
     }
     v3d = h->partials + (1 << 20) + 8192 + 65536;       // [(3C+1)^2]
-    rc = bax_syrk(h, h->Gv, 3 * C + 1, h->Nv, h->ldv, v3d, s); if (rc) return rc;
+    rc = bax_syrk_aug(h, h->Gv, 3 * C, 1, h->Nv, h->ldv, v3d, 3 * C + 1, s); if (rc) return rc;   // residual row rides along
   }
   k_lin_pack<<<64, 256, 0, s>>>(h->partials + (1 << 20), v3d, C, lin, h->B);
   BAX_LAUNCH_CHECK();

@@ -160,6 +160,7 @@ static void free_problem(bax_handle* h) {
   h->K = nullptr; h->bones = nullptr; h->joint_bones = nullptr; h->dhat = nullptr; h->blockbase = nullptr;
   h->campack = nullptr; h->campack_lin = nullptr; h->Vp = h->gp = h->Hcc = h->gc = h->Lbar = h->rb = nullptr;
   h->Yhat = h->Gv = h->syrk_part = h->dense_ws = h->coef = h->partials = nullptr;
+  h->syrk_part_bytes = 0;
 }
 
 extern "C" int bax_destroy(bax_handle* h) {
@@ -175,7 +176,7 @@ extern "C" int bax_destroy(bax_handle* h) {
 extern "C" int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B, const double* K,
                                const double* y2d, const double* s2d, const double* p3d, const double* s3d,
                                const int32_t* bones_host, double lambda1, double lambda2, void* stream) {
-  if (!h || C < 1 || N < 1 || J < 1 || B < 0 || B > BAX_MAX_B || !K || !y2d || !s2d || (B > 0 && !bones_host)) {
+  if (!h || C < 1 || N < 1 || J < 1 || B < 0 || B >= BAX_MAX_B || !K || !y2d || !s2d || (B > 0 && !bones_host)) {
     bax_set_error("bax_problem_set: bad argument"); return BAX_E_ARG;
   }
   cudaStream_t s = (cudaStream_t)stream;

@@ -162,7 +162,8 @@ extern "C" int bax_trial_begin(bax_handle* h, double alpha, void* stream) {
         h->s2d, h->P, C, h->J, h->B, h->bones, h->joint_bones, h->Lbar, scale, h->Vp, h->gp, alpha, h->Yhat, h->ldy);
     BAX_LAUNCH_CHECK();
   }
-  return bax_syrk(h, h->Yhat, h->R, 3 * h->P, h->ldy, h->buf[BAX_BUF_SCHUR], s);
+  // camera rows: dense SYRK on the FP64 tensor pipe; the B + 1 bone-length / right-hand-side rows ride along
+  return bax_syrk_aug(h, h->Yhat, 6 * C, h->B + 1, 3 * h->P, h->ldy, h->buf[BAX_BUF_SCHUR], h->R, s);
 }
 
 extern "C" int bax_trial_mid(bax_handle* h, double* step, int need_phi_prime, void* stream) {
