@@ -73,6 +73,7 @@ struct bax_handle {
   size_t partials_bytes;
   double* host_pinned;       // small pinned staging for scalars
   // ---- timing
+  int dense_coop;            // 1: cooperative multi-CTA reduced solve (env BAX_DENSE_COOP=0 selects the single-CTA kernel)
   int rj_variant;            // tuning knob (env BAX_RJ_VARIANT): 0 = per-warp staged LSU stores; 1/2/3 = CTA-staged TMA bulk stores (256x4, 128x8 [default], 256x3)
   int timing;
   cudaEvent_t ev0, ev1;
