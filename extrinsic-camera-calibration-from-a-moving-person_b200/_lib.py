@@ -25,6 +25,7 @@ _SIGS = {
     "bax_destroy": (i32, [vp]),
     "bax_problem_set": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, P_i32, f64, f64, vp]),
     "bax_problem_dims": (i32, [vp, P_i64]),
+    "bax_observations_rebind": (i32, [vp, vp, vp]),
     "bax_residual": (i32, [vp, vp, vp, vp]),
     "bax_residual_jacobian": (i32, [vp, vp, vp, vp, vp, vp, vp, vp]),
     "bax_prior_jacobian": (i32, [vp, vp, vp, vp, vp]),
@@ -37,6 +38,8 @@ _SIGS = {
     "bax_linearize_mid": (i32, [vp, vp]),
     "bax_linearize_post": (i32, [vp, vp]),
     "bax_linearize_finish": (i32, [vp, P_f64, vp]),
+    "bax_linearize_push": (i32, [vp]),
+    "bax_linearize_pop": (i32, [vp]),
     "bax_trial_begin": (i32, [vp, f64, vp]),
     "bax_trial_mid": (i32, [vp, vp, i32, vp]),
     "bax_trial_finish": (i32, [vp, P_f64, vp]),

@@ -134,6 +134,13 @@ class BAProblem:
         self.h_scale = 0.0
         self.n_trials = 0                     # damped solves so far (bench accounting)
 
+    def rebind_observations(self, y, s):
+        """Use another device copy of (sp2d, ss2d) — same shapes and visibility pattern — from now on."""
+        assert y.is_cuda and s.is_cuda and y.dtype == torch.float64 and s.dtype == torch.float64
+        assert y.numel() == self.y.numel() and s.numel() == self.s.numel() and y.is_contiguous() and s.is_contiguous()
+        check(self.L.bax_observations_rebind(self.h, y.data_ptr(), s.data_ptr()), "bax_observations_rebind")
+        self.y, self.s = y.reshape(self.C, self.P, 2), s.reshape(self.C, self.P)
+
     def close(self):
         if getattr(self, "h", None):
             self.L.bax_destroy(self.h)
@@ -155,10 +162,12 @@ class BAProblem:
         if self.group is None:
             return
         import torch.distributed as dist
-        if which not in self._views:
-            p, n = C.c_void_p(), C.c_int64()
-            check(self.L.bax_reduce_buffer(self.h, which, C.byref(p), C.byref(n)), "bax_reduce_buffer")
-            self._views[which] = torch.as_tensor(_DevView(p.value, n.value), device=self.dev)
+        p, n = C.c_void_p(), C.c_int64()
+        check(self.L.bax_reduce_buffer(self.h, which, C.byref(p), C.byref(n)), "bax_reduce_buffer")
+        key = (which, p.value)                 # the LIN buffer changes address on linearize_push / _pop
+        if key not in self._views:
+            self._views[key] = torch.as_tensor(_DevView(p.value, n.value), device=self.dev)
+        which = key
         dist.all_reduce(self._views[which], op=op or dist.ReduceOp.SUM, group=self.group)
 
     # ---- reference-shaped evaluations
@@ -266,6 +275,16 @@ class BAProblem:
             check(self.L.bax_linearize_finish(self.h, self._out4, st), "bax_linearize_finish")
         self.h_scale = self._out4[4]          # max diagonal of the point blocks of J^T J
         return tuple(self._out4[:4])
+
+    def linearize_push(self):
+        """Save the current linearisation; the next linearize() may run at a trial point."""
+        check(self.L.bax_linearize_push(self.h), "bax_linearize_push")
+        self._saved_lin = (getattr(self, "_keep_lin", None), self.h_scale)
+
+    def linearize_pop(self):
+        """Restore the linearisation saved by linearize_push() (the trial step was rejected)."""
+        check(self.L.bax_linearize_pop(self.h), "bax_linearize_pop")
+        self._keep_lin, self.h_scale = self._saved_lin
 
     def trial(self, alpha, need_phi_prime=True):
         """Solve (J^T J + alpha I) p = -g; p lands in self.step (device).
@@ -402,8 +421,11 @@ class TRFSolver:
     trust-region solves and cost evaluations until a step is accepted (or evaluations run out), then a
     re-linearisation."""
 
-    def __init__(self, prob, theta0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None):
+    def __init__(self, prob, theta0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, speculative=True):
         self.prob = prob
+        # speculative: a trial point is linearised straight away (its cost falls out of the linearisation), so an
+        # accepted step needs no separate cost pass; a rejected step restores the saved linearisation
+        self.speculative = speculative
         self.x = prob._dev_theta(theta0).clone()
         self.x_new = torch.empty_like(self.x)
         self.ftol, self.xtol, self.gtol = ftol, xtol, gtol
@@ -435,13 +457,22 @@ class TRFSolver:
             # -(0.5 ||J s||^2 + g.s) with s = kappa p and p^T J^T J p = -g.p - alpha ||p||^2
             predicted = -(0.5 * kappa * kappa * (-gdotp - alpha * p_norm * p_norm) + kappa * gdotp)
             torch.add(self.x, prob.step, alpha=kappa, out=self.x_new)
-            cost_new = prob.cost(self.x_new)
+            spec = self.speculative and relinearize
+            if spec:
+                prob.linearize_push()
+                cost_new, g_inf_new, g_2_new, x_norm_new = prob.linearize(self.x_new)
+            else:
+                cost_new = prob.cost(self.x_new)
             self.nfev += 1
             step_norm = kappa * p_norm
             if not math.isfinite(cost_new):
+                if spec:
+                    prob.linearize_pop()
                 self.Delta = 0.25 * step_norm
                 continue
             actual_reduction = self.cost - cost_new
+            if spec and not actual_reduction > 0:
+                prob.linearize_pop()
             Delta_new, ratio = _update_tr_radius(self.Delta, actual_reduction, predicted, step_norm,
                                                  step_norm > 0.95 * self.Delta)
             self.history.append(dict(alpha=alpha, Delta=self.Delta, step_norm=step_norm, cost_new=cost_new,
@@ -454,7 +485,10 @@ class TRFSolver:
             self.Delta = Delta_new
         if actual_reduction > 0:
             self.x, self.x_new = self.x_new, self.x
-            if relinearize:
+            if spec:
+                self.cost, self.g_inf, self.g_2, self.x_norm = cost_new, g_inf_new, g_2_new, x_norm_new
+                self.njev += 1
+            elif relinearize:
                 self.cost, self.g_inf, self.g_2, self.x_norm = prob.linearize(self.x)
                 self.njev += 1
             else:

@@ -54,6 +54,8 @@ struct bax_handle {
   double* Lbar;              // [B] mean bone lengths (global)
   double* rb;                // [B] lambda2 * Var_b
   double cost;
+  // saved copy of the linearisation (bax_linearize_push / _pop): the same fields, swapped by pointer
+  struct { double *Vp, *gp, *lin, *Lbar, *rb, *campack_lin; const double* theta_lin; double cost; int valid; } saved;
   // ---- trial state
   double alpha;
   int need_phi;               // last trial asked for phi'(alpha)

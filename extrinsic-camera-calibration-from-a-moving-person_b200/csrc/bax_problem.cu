@@ -155,12 +155,13 @@ extern "C" int bax_create(int device, bax_handle** out) {
 static void free_problem(bax_handle* h) {
   void* ptrs[] = {(void*)h->K, h->bones, h->joint_bones, h->dhat, h->blockbase, h->campack, h->campack_lin, h->Vp, h->gp,
                   h->Hcc, h->gc, h->Lbar, h->rb, h->Yhat, h->Gv, h->syrk_part, h->dense_ws, h->coef,
-                  h->partials};
+                  h->partials, h->saved.Vp, h->saved.gp, h->saved.lin, h->saved.Lbar, h->saved.rb, h->saved.campack_lin};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int i = 0; i < 8; ++i) { if (h->buf[i]) cudaFree(h->buf[i]); h->buf[i] = nullptr; }
   h->K = nullptr; h->bones = nullptr; h->joint_bones = nullptr; h->dhat = nullptr; h->blockbase = nullptr;
   h->campack = nullptr; h->campack_lin = nullptr; h->Vp = h->gp = h->Hcc = h->gc = h->Lbar = h->rb = nullptr;
   h->Yhat = h->Gv = h->syrk_part = h->dense_ws = h->coef = h->partials = nullptr;
+  h->saved.Vp = h->saved.gp = h->saved.lin = h->saved.Lbar = h->saved.rb = h->saved.campack_lin = nullptr; h->saved.valid = 0;
   h->syrk_part_bytes = 0;
 }
 
@@ -291,6 +292,43 @@ extern "C" int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B
   h->ldy = ((3 * h->P + 31) / 32) * 32;
   h->ldv = ((h->Nv + 31) / 32) * 32;
   BAX_CUDA(cudaStreamSynchronize(s));
+  return BAX_OK;
+}
+
+// Speculative linearisation (a trust-region step is linearised at the trial point straight away; a rejected step
+// restores the previous linearisation): push swaps the current state into the saved slot, pop swaps it back.
+static void swap_lin_state(bax_handle* h) {
+  auto sw = [](double*& a, double*& b) { double* t = a; a = b; b = t; };
+  sw(h->Vp, h->saved.Vp); sw(h->gp, h->saved.gp); sw(h->buf[BAX_BUF_LIN], h->saved.lin);
+  sw(h->Lbar, h->saved.Lbar); sw(h->rb, h->saved.rb); sw(h->campack_lin, h->saved.campack_lin);
+  const double* t = h->theta_lin; h->theta_lin = h->saved.theta_lin; h->saved.theta_lin = t;
+  double c = h->cost; h->cost = h->saved.cost; h->saved.cost = c;
+}
+extern "C" int bax_linearize_push(bax_handle* h) {
+  if (!h || !h->campack) { bax_set_error("bax_linearize_push: no problem"); return BAX_E_ARG; }
+  BAX_CUDA(cudaSetDevice(h->device));
+  if (!h->saved.Vp) {
+    BAX_CUDA(cudaMalloc(&h->saved.Vp, sizeof(double) * 6 * h->P));
+    BAX_CUDA(cudaMalloc(&h->saved.gp, sizeof(double) * 3 * h->P));
+    BAX_CUDA(cudaMalloc(&h->saved.lin, sizeof(double) * h->buf_count[BAX_BUF_LIN]));
+    BAX_CUDA(cudaMalloc(&h->saved.Lbar, sizeof(double) * BAX_MAX_B));
+    BAX_CUDA(cudaMalloc(&h->saved.rb, sizeof(double) * BAX_MAX_B));
+    BAX_CUDA(cudaMalloc(&h->saved.campack_lin, sizeof(double) * CAMPACK * h->C));
+  }
+  swap_lin_state(h);
+  h->saved.valid = 1;
+  return BAX_OK;
+}
+extern "C" int bax_linearize_pop(bax_handle* h) {
+  if (!h || !h->saved.valid) { bax_set_error("bax_linearize_pop: nothing pushed"); return BAX_E_STATE; }
+  swap_lin_state(h);
+  h->saved.valid = 0;
+  return BAX_OK;
+}
+
+extern "C" int bax_observations_rebind(bax_handle* h, const double* y2d, const double* s2d) {
+  if (!h || !h->campack || !y2d || !s2d) { bax_set_error("bax_observations_rebind: bad argument / no problem"); return BAX_E_ARG; }
+  h->y2d = y2d; h->s2d = s2d;
   return BAX_OK;
 }
 

@@ -40,6 +40,11 @@ int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B,
                     const double* p3d, const double* s3d, const int32_t* bones_host,
                     double lambda1, double lambda2, void* stream);
 
+/* Point the bound problem at another copy of the observations (same shapes, same visibility pattern s2d > 0): lets a
+ * caller upload the next batch into a second device buffer while kernels still read the first (double buffering of
+ * the host -> device stream).  Takes effect for calls issued afterwards. */
+int bax_observations_rebind(bax_handle* h, const double* y2d, const double* s2d);
+
 /* dims_host[0..5] = { n_vis (visible observations), n_v3d (valid orientation rows),
  *                     m (residual rows), n (parameters), aug_rows (6C+13), n_points } */
 int bax_problem_dims(bax_handle* h, int64_t* dims_host);
@@ -83,6 +88,12 @@ int bax_linearize_begin(bax_handle* h, const double* theta, void* stream); /* fi
 int bax_linearize_mid(bax_handle* h, void* stream);                        /* fills BAX_BUF_LIN  */
 int bax_linearize_post(bax_handle* h, void* stream);   /* fills BAX_BUF_NORM (sum) and BAX_BUF_GMAX (max) */
 int bax_linearize_finish(bax_handle* h, double* out_host, void* stream);   /* synchronises       */
+
+/* Speculative linearisation: bax_linearize_push() saves the current linearisation (pointer swap, no copy) so that
+ * the next bax_linearize_* sequence can run at a trial point; bax_linearize_pop() restores the saved one if that
+ * trial step is rejected.  After a push the BAX_BUF_LIN reduce buffer has a different address (query it again). */
+int bax_linearize_push(bax_handle* h);
+int bax_linearize_pop(bax_handle* h);
 
 /* One damped solve (J^T J + alpha I) p = -g through the per-point Schur complement with the
  * rank-B Woodbury correction for the bone-length rows; alpha > 0.
