@@ -22,6 +22,32 @@ k_rsx_fit(int C, int64_t N, int64_t M, const double* __restrict__ v, const doubl
     fit_hypothesis(g, C, N, M, v, n, samp_v + h * RSX_S, samp_m + h * RSX_S, ws, Rt + (size_t)h * C * 12);
 }
 
+// One WARP per hypothesis (few cameras): the arrow-structured subspace iteration of rsx_arrow.cuh needs only warp-wide
+// steps, so FITW_WARPS hypotheses share a CTA, each with its own shared-memory workspace, and __syncwarp replaces the
+// CTA barrier.  A hypothesis whose iteration does not settle is finished by the same warp with the Jacobi solver.
+#define FITW_WARPS 2
+__global__ void __launch_bounds__(32 * FITW_WARPS)
+k_rsx_fit_warp(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
+               const int32_t* __restrict__ samp_v, const int32_t* __restrict__ samp_m, int64_t H,
+               double* __restrict__ Rt, unsigned long long* __restrict__ stats /*[2]: fall-backs, sweeps*/) {
+  extern __shared__ __align__(16) double sm[];
+  const int nu = 3 * (RSX_S + C), ld = nu | 1;
+  const size_t per_warp = (fit_ws_small_doubles(C) + 2 * (size_t)nu * ld + 1) & ~(size_t)1;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  FitWs ws;
+  fit_ws_carve(sm + warp * per_warp, nullptr, C, ws);
+  WarpCtx g{lane, 32};
+  const int64_t stride = (int64_t)gridDim.x * FITW_WARPS;
+  for (int64_t h = (int64_t)blockIdx.x * FITW_WARPS + warp; h < H; h += stride) {
+    fit_hypothesis(g, C, N, M, v, n, samp_v + h * RSX_S, samp_m + h * RSX_S, ws, Rt + (size_t)h * C * 12, true);
+    if (stats && lane == 0) {
+      const int sw = ws.iflag[8];
+      if (sw < 0) atomicAdd(stats, 1ULL); else atomicAdd(stats + 1, (unsigned long long)sw);
+    }
+    __syncwarp();
+  }
+}
+
 __global__ void __launch_bounds__(SCORE_THREADS)
 k_rsx_score(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
             const double* __restrict__ Rt, int64_t H, double* __restrict__ score, double* __restrict__ parts) {
@@ -102,6 +128,9 @@ extern "C" int rsx_create(int device, rsx_handle** out) {
   BAX_CUDA(cudaMallocHost((void**)&h->host_pinned, 64 * sizeof(double)));
   h->red_bytes = sizeof(double) * (1 << 20);
   BAX_CUDA(cudaMalloc(&h->red, h->red_bytes));
+  { const char* e = getenv("RSX_FIT_MODE"); h->fit_mode = e ? atoi(e) : 1; }   // 0: CTA Jacobi kernel only
+  BAX_CUDA(cudaMalloc(&h->fit_stats, 2 * sizeof(unsigned long long)));
+  BAX_CUDA(cudaMemset(h->fit_stats, 0, 2 * sizeof(unsigned long long)));
   h->bx = (bax_handle*)calloc(1, sizeof(bax_handle));
   h->bx->device = device; h->bx->sm_count = h->sm_count;
   *out = h;
@@ -119,7 +148,7 @@ extern "C" int rsx_destroy(rsx_handle* h) {
   cudaSetDevice(h->device);
   rsx_free_problem(h);
   if (h->bx) { if (h->bx->syrk_part) cudaFree(h->bx->syrk_part); if (h->bx->partials) cudaFree(h->bx->partials); free(h->bx); }
-  cudaFree(h->red); cudaFreeHost(h->host_pinned);
+  cudaFree(h->red); cudaFree(h->fit_stats); cudaFreeHost(h->host_pinned);
   cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
   free(h);
   return BAX_OK;
@@ -155,6 +184,22 @@ int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, 
   const int C = h->C, nu = 3 * (RSX_S + C), ld = nu | 1;
   const size_t small = fit_ws_small_doubles(C) * sizeof(double);
   const size_t hv = sizeof(double) * 2 * (size_t)nu * ld;
+  {  // few cameras: one warp per hypothesis
+    const size_t per_warp = ((fit_ws_small_doubles(C) + 2 * (size_t)nu * ld + 1) & ~(size_t)1) * sizeof(double);
+    const size_t smem = per_warp * FITW_WARPS;
+    if (h->fit_mode != 0 && smem <= 110 * 1024 && arrow_ws_doubles(C, 32) <= (size_t)nu * ld) {
+      const int per_sm = (int)((220 * 1024) / smem);
+      int64_t grid = (H + FITW_WARPS - 1) / FITW_WARPS;
+      const int64_t cap = (int64_t)h->sm_count * per_sm * 4;
+      if (grid > cap) grid = cap;
+      BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_warp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      RsxTimer t(h, RSX_T_FIT, s, 1);
+      k_rsx_fit_warp<<<(unsigned)grid, 32 * FITW_WARPS, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt,
+                                                                   (unsigned long long*)h->fit_stats);
+      BAX_LAUNCH_CHECK();
+      return BAX_OK;
+    }
+  }
   int64_t grid = H;
   double* hvg = nullptr;
   size_t smem = small + hv;

@@ -1,0 +1,259 @@
+// The 4-dimensional invariant subspace of the smallest eigenvalues of the translation normal matrix H of one
+// minimal sample (reference calib_ransac.py:96-107 takes it from a dense LAPACK eigh), by inverse subspace
+// iteration that exploits H's arrow structure:
+//
+//   H = [ D  B ]   D = blockdiag(D_0..D_9), 3x3 (one per sampled ray),  B: 30 x 3C,  T: 3C x 3C
+//       [ B' T ]
+//   (H + s I)^-1 is applied through  D_i + s I = L_i L_i',  W_i = L_i^-1 B_i,  S = T + s I - sum_i W_i' W_i = Ls Ls'.
+//
+// For the minimal samples of this path lambda_4 / lambda_5 has median 0.013 and stays below ~0.2, so 6-20 sweeps
+// reach round-off; a parallel Jacobi diagonalisation of the same 42 x 42 matrix costs ~50x the flops.  Any basis of
+// the subspace serves the caller (it only needs the combination whose t_0 block vanishes).  Returns false when
+// the sweep count runs out (pathological gap, NaN data): the caller then falls back to the Jacobi solver, so the
+// result never depends on this shortcut converging.
+//
+// Written against the same cooperating-group context as rsx_fit.cuh (tid, nt, sync()); group-wide sums go through
+// a [k][nt] scratch, so the code runs unchanged on one warp of the GPU and single-threaded on the host.
+#pragma once
+#include "rsx_internal.cuh"
+
+#define ARW_K 4            // subspace dimension
+#define ARW_MAX_SWEEPS 48
+
+struct ArrowWs {
+  double* Ld;    // [10][9]  l00 l10 l11 l20 l21 l22 | 1/l00 1/l11 1/l22
+  double* Wm;    // [30][3C]
+  double* S;     // [3C][3C] lower Cholesky factor of the Schur complement
+  double* rS;    // [3C]     reciprocal diagonal of that factor
+  double* Q;     // [nu][4]
+  double* Z;     // [nu][4]
+  double* red;   // [16][nt] reduction scratch
+  double* out;   // [32]     reduction results / small shared scalars
+};
+__host__ __device__ inline size_t arrow_ws_doubles(int C, int nt) {
+  const int nu = 3 * (RSX_S + C), n3 = 3 * C;
+  return 90 + (size_t)30 * n3 + (size_t)n3 * n3 + n3 + 2 * (size_t)nu * ARW_K + 16 * (size_t)nt + 32;
+}
+__host__ __device__ inline void arrow_ws_carve(double* p, int C, int nt, ArrowWs& a) {
+  const int nu = 3 * (RSX_S + C), n3 = 3 * C;
+  a.Ld = p; p += 90; a.Wm = p; p += 30 * n3; a.S = p; p += n3 * n3; a.rS = p; p += n3;
+  a.Q = p; p += nu * ARW_K; a.Z = p; p += nu * ARW_K; a.red = p; p += 16 * nt; a.out = p;
+}
+
+// out[j] = sum over the group of vals[j], j < k <= 16 (every thread reads the same out[] afterwards)
+template <class G>
+__host__ __device__ inline void group_sum(const G& g, const double* vals, int k, double* red, double* out) {
+  for (int j = 0; j < k; ++j) red[j * g.nt + g.tid] = vals[j];
+  g.sync();
+  for (int j = g.tid; j < k; j += g.nt) {
+    double s = 0.0;
+    for (int t = 0; t < g.nt; ++t) s += red[j * g.nt + t];
+    out[j] = s;
+  }
+  g.sync();
+}
+
+// Z <- orthonormal basis of span(Z) by Cholesky QR (Gram matrix -> 4x4 Cholesky -> Z R^-1); called twice per sweep,
+// the second pass removes the O(eps cond^2) loss of orthogonality of the first.  Returns false on a non-positive pivot.
+template <class G>
+__host__ __device__ inline bool cholqr4(const G& g, double* Z, int nu, double* red, double* out) {
+  double p[10];
+  for (int e = 0; e < 10; ++e) p[e] = 0.0;
+  for (int i = g.tid; i < nu; i += g.nt) {
+    const double* z = Z + i * ARW_K;
+    int e = 0;
+    for (int a = 0; a < ARW_K; ++a)
+      for (int b = a; b < ARW_K; ++b) p[e++] += z[a] * z[b];
+  }
+  group_sum(g, p, 10, red, out);
+  // upper Cholesky factor R (Gram = R' R), computed redundantly by every thread
+  const double m00 = out[0], m01 = out[1], m02 = out[2], m03 = out[3], m11 = out[4], m12 = out[5], m13 = out[6],
+               m22 = out[7], m23 = out[8], m33 = out[9];
+  if (!(m00 > 0)) return false;
+  const double i0 = rsx_rsqrt(m00);
+  const double r01 = m01 * i0, r02 = m02 * i0, r03 = m03 * i0;
+  const double d1 = m11 - r01 * r01;
+  if (!(d1 > 0)) return false;
+  const double i1 = rsx_rsqrt(d1);
+  const double r12 = (m12 - r01 * r02) * i1, r13 = (m13 - r01 * r03) * i1;
+  const double d2 = m22 - r02 * r02 - r12 * r12;
+  if (!(d2 > 0)) return false;
+  const double i2 = rsx_rsqrt(d2);
+  const double r23 = (m23 - r02 * r03 - r12 * r13) * i2;
+  const double d3 = m33 - r03 * r03 - r13 * r13 - r23 * r23;
+  if (!(d3 > 0)) return false;
+  const double i3 = rsx_rsqrt(d3);
+  g.sync();                                              // everyone has read out[] before it is reused
+  for (int i = g.tid; i < nu; i += g.nt) {               // row z <- z R^-1 (forward substitution along the row)
+    double* z = Z + i * ARW_K;
+    const double q0 = z[0] * i0;
+    const double q1 = (z[1] - q0 * r01) * i1;
+    const double q2 = (z[2] - q0 * r02 - q1 * r12) * i2;
+    const double q3 = (z[3] - q0 * r03 - q1 * r13 - q2 * r23) * i3;
+    z[0] = q0; z[1] = q1; z[2] = q2; z[3] = q3;
+  }
+  g.sync();
+  return true;
+}
+
+// H: [nu][ld] dense symmetric (read only), R: [C][9] rotations (for the start vectors), kb: [nu][4] basis out.
+template <class G>
+__host__ __device__ inline bool arrow_null4(const G& g, const double* H, int ld, int C, const double* R,
+                                            const ArrowWs& a, double* kb, int* sweeps_out) {
+  const int n3 = 3 * C, T0 = 3 * RSX_S, nu = T0 + n3;
+  // ---- shift: far below lambda_1 (>= 1e-7 of the mean diagonal here), far above the round-off of the factorisation
+  double tr[1] = {0.0};
+  for (int i = g.tid; i < nu; i += g.nt) tr[0] += H[i * ld + i];
+  group_sum(g, tr, 1, a.red, a.out);
+  const double sig = 1e-13 * a.out[0] / nu;
+  if (!(sig > 0)) return false;
+  g.sync();
+  // ---- D_i + sig I = L_i L_i'
+  for (int i = g.tid; i < RSX_S; i += g.nt) {
+    const double* d = H + (3 * i) * ld + 3 * i;
+    double* o = a.Ld + 9 * i;
+    const double i0 = rsx_rsqrt(d[0] + sig);
+    const double l10 = d[ld] * i0, l20 = d[2 * ld] * i0;
+    const double i1 = rsx_rsqrt(d[ld + 1] + sig - l10 * l10);
+    const double l21 = (d[2 * ld + 1] - l20 * l10) * i1;
+    const double i2 = rsx_rsqrt(d[2 * ld + 2] + sig - l20 * l20 - l21 * l21);
+    o[0] = (d[0] + sig) * i0; o[1] = l10; o[2] = (d[ld + 1] + sig - l10 * l10) * i1; o[3] = l20; o[4] = l21;
+    o[5] = (d[2 * ld + 2] + sig - l20 * l20 - l21 * l21) * i2; o[6] = i0; o[7] = i1; o[8] = i2;
+  }
+  g.sync();
+  // ---- W_i = L_i^-1 B_i
+  for (int t = g.tid; t < RSX_S * n3; t += g.nt) {
+    const int i = t / n3, c = t - i * n3;
+    const double* L = a.Ld + 9 * i;
+    const double b0 = H[(3 * i) * ld + T0 + c], b1 = H[(3 * i + 1) * ld + T0 + c], b2 = H[(3 * i + 2) * ld + T0 + c];
+    const double w0 = b0 * L[6];
+    const double w1 = (b1 - L[1] * w0) * L[7];
+    const double w2 = (b2 - L[3] * w0 - L[4] * w1) * L[8];
+    a.Wm[(3 * i) * n3 + c] = w0; a.Wm[(3 * i + 1) * n3 + c] = w1; a.Wm[(3 * i + 2) * n3 + c] = w2;
+  }
+  g.sync();
+  // ---- S = T + sig I - W' W (lower part), then its Cholesky factor in place
+  for (int t = g.tid; t < n3 * n3; t += g.nt) {
+    const int r = t / n3, c = t - r * n3;
+    if (c > r) continue;
+    double s = H[(T0 + r) * ld + T0 + c] + (r == c ? sig : 0.0);
+    for (int k = 0; k < 3 * RSX_S; ++k) s -= a.Wm[k * n3 + r] * a.Wm[k * n3 + c];
+    a.S[r * n3 + c] = s;
+  }
+  g.sync();
+  for (int k = 0; k < n3; ++k) {
+    const double dk = a.S[k * n3 + k];
+    if (!(dk > 0)) return false;                                   // same value in every thread
+    const double ik = rsx_rsqrt(dk);
+    g.sync();
+    for (int j = k + g.tid; j < n3; j += g.nt) {
+      if (j == k) { a.S[k * n3 + k] = dk * ik; a.rS[k] = ik; }
+      else a.S[j * n3 + k] *= ik;
+    }
+    g.sync();
+    const int w = n3 - k - 1;
+    for (int t = g.tid; t < w * w; t += g.nt) {
+      const int r = k + 1 + t / w, c = k + 1 + t % w;
+      if (c <= r) a.S[r * n3 + c] -= a.S[r * n3 + k] * a.S[c * n3 + k];
+    }
+    g.sync();
+  }
+  // ---- start: the three world shifts (exact null vectors of the collinearity rows: X_i += d, t_c -= R_c d) and one
+  // fixed pseudo-random vector for the scale-like direction
+  for (int i = g.tid; i < nu; i += g.nt) {
+    double* q = a.Q + i * ARW_K;
+    if (i < T0) { q[0] = (i % 3 == 0); q[1] = (i % 3 == 1); q[2] = (i % 3 == 2); }
+    else { const int c = (i - T0) / 3, r = (i - T0) % 3; q[0] = -R[9 * c + 3 * r]; q[1] = -R[9 * c + 3 * r + 1]; q[2] = -R[9 * c + 3 * r + 2]; }
+    const unsigned hsh = (unsigned)(i + 1) * 2654435761u;
+    q[3] = (double)(hsh >> 8) * (1.0 / 16777216.0) - 0.5;
+  }
+  g.sync();
+  if (!cholqr4(g, a.Q, nu, a.red, a.out)) return false;
+  if (!cholqr4(g, a.Q, nu, a.red, a.out)) return false;
+  double prev = 1e300;
+  bool done = false;
+  int sweep = 0;
+  for (; sweep < ARW_MAX_SWEEPS && !done; ++sweep) {
+    // ---- Z = (H + sig I)^-1 Q by block elimination
+    for (int t = g.tid; t < RSX_S * ARW_K; t += g.nt) {            // y_i = L_i^-1 q_i
+      const int i = t / ARW_K, v = t - i * ARW_K;
+      const double* L = a.Ld + 9 * i;
+      const double y0 = a.Q[(3 * i) * ARW_K + v] * L[6];
+      const double y1 = (a.Q[(3 * i + 1) * ARW_K + v] - L[1] * y0) * L[7];
+      const double y2 = (a.Q[(3 * i + 2) * ARW_K + v] - L[3] * y0 - L[4] * y1) * L[8];
+      a.Z[(3 * i) * ARW_K + v] = y0; a.Z[(3 * i + 1) * ARW_K + v] = y1; a.Z[(3 * i + 2) * ARW_K + v] = y2;
+    }
+    g.sync();
+    for (int t = g.tid; t < n3 * ARW_K; t += g.nt) {               // r = q_t - W' y
+      const int r = t / ARW_K, v = t - r * ARW_K;
+      double s = a.Q[(T0 + r) * ARW_K + v];
+      for (int k = 0; k < 3 * RSX_S; ++k) s -= a.Wm[k * n3 + r] * a.Z[k * ARW_K + v];
+      a.Z[(T0 + r) * ARW_K + v] = s;
+    }
+    g.sync();
+    for (int v = g.tid; v < ARW_K; v += g.nt) {                    // x_t = S^-1 r, one vector per thread
+      double* z = a.Z + T0 * ARW_K + v;
+      for (int r = 0; r < n3; ++r) {
+        double s = z[r * ARW_K];
+        for (int k = 0; k < r; ++k) s -= a.S[r * n3 + k] * z[k * ARW_K];
+        z[r * ARW_K] = s * a.rS[r];
+      }
+      for (int r = n3 - 1; r >= 0; --r) {
+        double s = z[r * ARW_K];
+        for (int k = r + 1; k < n3; ++k) s -= a.S[k * n3 + r] * z[k * ARW_K];
+        z[r * ARW_K] = s * a.rS[r];
+      }
+    }
+    g.sync();
+    for (int t = g.tid; t < RSX_S * ARW_K; t += g.nt) {            // x_i = L_i^-T (y_i - W_i x_t)
+      const int i = t / ARW_K, v = t - i * ARW_K;
+      const double* L = a.Ld + 9 * i;
+      double y0 = a.Z[(3 * i) * ARW_K + v], y1 = a.Z[(3 * i + 1) * ARW_K + v], y2 = a.Z[(3 * i + 2) * ARW_K + v];
+      for (int c = 0; c < n3; ++c) {
+        const double xt = a.Z[(T0 + c) * ARW_K + v];
+        y0 -= a.Wm[(3 * i) * n3 + c] * xt; y1 -= a.Wm[(3 * i + 1) * n3 + c] * xt; y2 -= a.Wm[(3 * i + 2) * n3 + c] * xt;
+      }
+      const double x2 = y2 * L[8];
+      const double x1 = (y1 - L[4] * x2) * L[7];
+      const double x0 = (y0 - L[1] * x1 - L[3] * x2) * L[6];
+      a.Z[(3 * i) * ARW_K + v] = x0; a.Z[(3 * i + 1) * ARW_K + v] = x1; a.Z[(3 * i + 2) * ARW_K + v] = x2;
+    }
+    g.sync();
+    if (!cholqr4(g, a.Z, nu, a.red, a.out)) return false;
+    if (!cholqr4(g, a.Z, nu, a.red, a.out)) return false;
+    // ---- change of the subspace: || Z - Q (Q' Z) ||_F^2
+    double gm[16];
+    for (int e = 0; e < 16; ++e) gm[e] = 0.0;
+    for (int i = g.tid; i < nu; i += g.nt)
+      for (int p = 0; p < ARW_K; ++p)
+        for (int q = 0; q < ARW_K; ++q) gm[4 * p + q] += a.Q[i * ARW_K + p] * a.Z[i * ARW_K + q];
+    group_sum(g, gm, 16, a.red, a.out);
+    for (int e = 0; e < 16; ++e) gm[e] = a.out[e];
+    g.sync();
+    double er[1] = {0.0};
+    for (int i = g.tid; i < nu; i += g.nt)
+      for (int q = 0; q < ARW_K; ++q) {
+        double d = a.Z[i * ARW_K + q];
+        for (int p = 0; p < ARW_K; ++p) d -= a.Q[i * ARW_K + p] * gm[4 * p + q];
+        er[0] += d * d;
+      }
+    group_sum(g, er, 1, a.red, a.out);
+    const double err2 = a.out[0];
+    g.sync();
+    for (int i = g.tid; i < nu * ARW_K; i += g.nt) a.Q[i] = a.Z[i];
+    g.sync();
+    // settled: the subspace moved by less than 1e-12 (the error left is that times rho / (1 - rho)), or it sits on
+    // the round-off floor of the solves (tiny and no longer contracting)
+#if defined(ARW_DEBUG) && !defined(__CUDA_ARCH__)
+    printf("  sweep %d err2 %.3e\n", sweep, err2);
+#endif
+    done = (err2 < 1e-24) || (err2 < 1e-21 && err2 > 0.81 * prev);
+    if (!(err2 == err2)) return false;                             // NaN
+    prev = err2;
+  }
+  if (sweeps_out) *sweeps_out = sweep;
+  if (!done) return false;
+  for (int i = g.tid; i < nu * ARW_K; i += g.nt) kb[i] = a.Q[i];
+  g.sync();
+  return true;
+}

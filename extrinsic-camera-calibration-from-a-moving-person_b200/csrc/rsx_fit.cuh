@@ -1,6 +1,7 @@
 // calib_linear on one minimal sample (reference calib_ransac.py:51-131), executed by one thread group.
 #pragma once
 #include "rsx_internal.cuh"
+#include "rsx_arrow.cuh"
 
 // Workspace of one hypothesis (shared memory; H and V may live in global memory for many cameras).
 struct FitWs {
@@ -14,17 +15,18 @@ struct FitWs {
   double* V;     // [nu][ld]   its eigenvectors
   double* cs;    // [nu/2 + 1][2] rotation pairs; later u [nu]
   double* misc;  // [64]
+  double* kb;    // [nu][4]   basis of the 4 smallest eigen-directions of H
   int* iflag;    // [8]
 };
 __host__ __device__ inline size_t fit_ws_small_doubles(int C) {      // everything but H, V
   const int nu = 3 * (RSX_S + C);
-  return (size_t)C * 30 * 3 + 9 * C + 2 * 110 + 2 * (nu / 2 + 1) + nu + 64 + 8;
+  return (size_t)C * 30 * 3 + 9 * C + 2 * 110 + 2 * (nu / 2 + 1) + nu + 64 + 4 * nu + 8;
 }
 __host__ __device__ inline void fit_ws_carve(double* base, double* HV /*null: carve from base*/, int C, FitWs& ws) {
   const int nu = 3 * (RSX_S + C), ld = nu | 1;
   double* p = base;
   ws.vs = p; p += C * 30; ws.ns = p; p += C * 30; ws.w = p; p += C * 30; ws.R = p; p += 9 * C;
-  ws.G = p; p += 110; ws.GV = p; p += 110; ws.cs = p; p += 2 * (nu / 2 + 1) + nu; ws.misc = p; p += 64;
+  ws.G = p; p += 110; ws.GV = p; p += 110; ws.cs = p; p += 2 * (nu / 2 + 1) + nu; ws.misc = p; p += 64; ws.kb = p; p += 4 * nu;
   ws.iflag = (int*)p; p += 8;
   if (HV) { ws.H = HV; ws.V = HV + (size_t)nu * ld; }
   else { ws.H = p; ws.V = p + (size_t)nu * ld; }
@@ -34,7 +36,8 @@ __host__ __device__ inline void fit_ws_carve(double* base, double* HV /*null: ca
 template <class G>
 __host__ __device__ inline void fit_hypothesis(const G& g, int C, int64_t N, int64_t M, const double* __restrict__ v,
                                                const double* __restrict__ n, const int32_t* __restrict__ sv,
-                                               const int32_t* __restrict__ sm, const FitWs& ws, double* Rt_out) {
+                                               const int32_t* __restrict__ sm, const FitWs& ws, double* Rt_out,
+                                               bool fast = true) {
   const int nu = 3 * (RSX_S + C), ld = nu | 1, T0 = 3 * RSX_S;
   // ---- 1. gather the sample
   for (int idx = g.tid; idx < C * 30; idx += g.nt) {
@@ -163,26 +166,42 @@ __host__ __device__ inline void fit_hypothesis(const G& g, int C, int64_t N, int
       }
   }
   g.sync();
-  // ---- 4. the four eigenvectors of the smallest eigenvalues (calib_ransac.py:96-107)
-  cta_jacobi(g, ws.H, ws.V, nu, ld, ws.cs, ws.iflag, 40);
-  if (g.tid == 0) {
-    int sel[4] = {-1, -1, -1, -1};
-    for (int pass = 0; pass < 4; ++pass) {
-      int bi = -1; double bv = 0;
-      for (int i = 0; i < nu; ++i) {
-        bool used = false;
-        for (int q = 0; q < pass; ++q) used |= (sel[q] == i);
-        if (used) continue;
-        const double e = ws.H[i * ld + i];
-        if (bi < 0 || e < bv) { bi = i; bv = e; }
+  // ---- 4. the four eigenvectors of the smallest eigenvalues (calib_ransac.py:96-107): only their span matters below.
+  // Small groups (one warp / the host) first try the arrow-structured inverse subspace iteration, whose workspace
+  // lives in V; the Jacobi diagonalisation of H remains the general path and the fall-back.
+  bool have_kb = false;
+  if (fast && g.nt <= 32 && arrow_ws_doubles(C, g.nt) <= (size_t)nu * ld) {
+    ArrowWs aw; arrow_ws_carve(ws.V, C, g.nt, aw);
+    have_kb = arrow_null4(g, ws.H, ld, C, ws.R, aw, ws.kb, ws.iflag + 8);
+    if (!have_kb && g.tid == 0) ws.iflag[8] = -1;
+  }
+  if (!have_kb) {
+    cta_jacobi(g, ws.H, ws.V, nu, ld, ws.cs, ws.iflag, 40);
+    if (g.tid == 0) {
+      int sel[4] = {-1, -1, -1, -1};
+      for (int pass = 0; pass < 4; ++pass) {
+        int bi = -1; double bv = 0;
+        for (int i = 0; i < nu; ++i) {
+          bool used = false;
+          for (int q = 0; q < pass; ++q) used |= (sel[q] == i);
+          if (used) continue;
+          const double e = ws.H[i * ld + i];
+          if (bi < 0 || e < bv) { bi = i; bv = e; }
+        }
+        sel[pass] = bi;
       }
-      sel[pass] = bi;
+      for (int j = 0; j < 4; ++j) ws.iflag[4 + j] = sel[j];
     }
+    g.sync();
+    for (int idx = g.tid; idx < nu * 4; idx += g.nt) ws.kb[idx] = ws.V[(idx >> 2) * ld + ws.iflag[4 + (idx & 3)]];
+    g.sync();
+  }
+  if (g.tid == 0) {
     // coefficients that make t_0 = 0: null vector of the 3x4 block k[t_0 rows, :]  (calib_ransac.py:110-111);
     // the SVD's unit norm and sign cancel in the scaling by |t_1| and the z-test below.
     double Kt[3][4];
     for (int r = 0; r < 3; ++r)
-      for (int j = 0; j < 4; ++j) Kt[r][j] = ws.V[(T0 + r) * ld + sel[j]];
+      for (int j = 0; j < 4; ++j) Kt[r][j] = ws.kb[(T0 + r) * 4 + j];
     double cf[4];
     for (int j = 0; j < 4; ++j) {
       double mnr[9]; int cc = 0;
@@ -193,13 +212,13 @@ __host__ __device__ inline void fit_hypothesis(const G& g, int C, int64_t N, int
       }
       cf[j] = ((j & 1) ? -1.0 : 1.0) * det3(mnr);
     }
-    for (int j = 0; j < 4; ++j) { ws.misc[j] = cf[j]; ws.iflag[4 + j] = sel[j]; }
+    for (int j = 0; j < 4; ++j) ws.misc[j] = cf[j];
   }
   g.sync();
   double* u = ws.cs;                                           // [nu] (rotation pairs no longer needed)
   for (int i = g.tid; i < nu; i += g.nt) {
     double acc = 0.0;
-    for (int j = 0; j < 4; ++j) acc += ws.V[i * ld + ws.iflag[4 + j]] * ws.misc[j];
+    for (int j = 0; j < 4; ++j) acc += ws.kb[i * 4 + j] * ws.misc[j];
     u[i] = acc;
   }
   g.sync();
@@ -262,9 +281,8 @@ __host__ __device__ inline double score_points(const G& g, int C, int64_t M, con
       const double* nn = n + ((size_t)c * M + i) * 3;
       dlt_accumulate(Rt + 12 * c, nn[0], nn[1], m);
     }
-    double a[4][4], X[4];
-    sym10_to_full(m, a);
-    eig4_smallest(a, X);
+    double X[4];
+    eig4_smallest_fast(m, X);
     bool inl = true;
     for (int c = 0; c < C; ++c) {
       const double* nn = n + ((size_t)c * M + i) * 3;

@@ -21,6 +21,13 @@ extern "C" void emu_eig4(const double* A16, double* x4) {
   eig4_smallest(a, x);
   for (int i = 0; i < 4; ++i) x4[i] = x[i];
 }
+extern "C" void emu_eig4_fast(const double* A16, double* x4) {
+  double m[10], x[4];
+  int e = 0;
+  for (int i = 0; i < 4; ++i) for (int j = i; j < 4; ++j) m[e++] = A16[4 * i + j];
+  eig4_smallest_fast(m, x);
+  for (int i = 0; i < 4; ++i) x4[i] = x[i];
+}
 extern "C" void emu_fit(int C, long long N, long long M, const double* v, const double* n, const int* sv, const int* sm,
                         double* Rt_out) {
   const int nu = 3 * (RSX_S + C), ld = nu | 1;
@@ -28,6 +35,17 @@ extern "C" void emu_fit(int C, long long N, long long M, const double* v, const 
   FitWs ws; fit_ws_carve(buf.data(), nullptr, C, ws);
   CtaCtx g{0, 1};
   fit_hypothesis(g, C, N, M, v, n, sv, sm, ws, Rt_out);
+}
+// mode 0: Jacobi only; 1: arrow subspace iteration first.  Returns the sweep count of the arrow path (-1: fell back).
+extern "C" int emu_fit_mode(int C, long long N, long long M, const double* v, const double* n, const int* sv, const int* sm,
+                            double* Rt_out, int mode) {
+  const int nu = 3 * (RSX_S + C), ld = nu | 1;
+  std::vector<double> buf(fit_ws_small_doubles(C) + 2 * (size_t)nu * ld);
+  FitWs ws; fit_ws_carve(buf.data(), nullptr, C, ws);
+  ws.iflag[8] = -2;
+  CtaCtx g{0, 1};
+  fit_hypothesis(g, C, N, M, v, n, sv, sm, ws, Rt_out, mode != 0);
+  return ws.iflag[8];
 }
 extern "C" void emu_score(int C, long long N, long long M, const double* v, const double* n, const double* Rt,
                           double* parts2, double* e_out, double* e3d_out, const double* K00, double th2d, double th3d,

@@ -120,6 +120,29 @@ def test_emulated_eig4(emu):
         assert abs(x @ A @ x - w[0]) <= 1e-12 * w[3]
 
 
+def test_emulated_eig4_inverse_iteration(emu):
+    """Cholesky inverse iteration (the scoring kernel's DLT solver): random matrices (poor gaps -> Jacobi fall-back),
+    DLT-like matrices with a small smallest eigenvalue, rank-deficient ones (3 rows) and NaN input."""
+    rng = np.random.default_rng(1)
+    for k in range(400):
+        B = rng.normal(size=(rng.integers(3, 9), 4))
+        if k % 2:                                   # triangulation-like: one direction nearly in the null space
+            u, sv, vt = np.linalg.svd(rng.normal(size=(8, 4)), full_matrices=False)
+            sv[3] = sv[2] * 10.0 ** rng.uniform(-8, -1)
+            B = (u * sv) @ vt
+        A = B.T @ B
+        x = np.zeros(4)
+        emu.emu_eig4_fast(dp(np.ascontiguousarray(A)), dp(x))
+        w, v = np.linalg.eigh(A)
+        assert abs(np.linalg.norm(x) - 1) < 1e-12
+        assert abs(abs(x @ v[:, 0]) - 1) < 1e-9 or w[1] - w[0] < 1e-6 * w[3]
+        assert abs(x @ A @ x - w[0]) <= 1e-12 * w[3]
+        if k % 2:
+            assert np.linalg.norm(x * np.sign(x @ v[:, 0]) - v[:, 0]) < 1e-12 * max(1.0, w[3] / (w[1] - w[0]))
+    x = np.zeros(4)
+    emu.emu_eig4_fast(dp(np.full((4, 4), np.nan)), dp(x))      # must terminate
+
+
 @pytest.mark.parametrize("case", ["c4", "c3"])
 def test_emulated_fit_score_masks_vs_reference_golden(emu, golden_dir, case):
     g = np.load(os.path.join(golden_dir, f"ransac_{case}.npz"))
