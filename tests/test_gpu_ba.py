@@ -210,3 +210,113 @@ def test_large_scene_properties():
     resid = J.T @ (J @ p) + alpha * p + grad
     assert np.linalg.norm(resid) <= 1e-8 * np.linalg.norm(grad)
     assert abs(gp - grad @ p) <= 1e-9 * abs(gp)
+
+
+# ----------------------------------------------------------------------------- paths added after the first GPU pass
+@pytest.mark.parametrize("case", ["small", "partial", "gafa_lambda"])
+def test_speculative_linearisation_same_path(golden_dir, case):
+    """Linearising the trial point straight away (push / pop of the linearisation state) must walk exactly the
+    iteration sequence of the cost-then-relinearise flow, rejected steps included."""
+    g, args, prob = _load(golden_dir, case)
+    hist = []
+    for spec in (False, True):
+        sol = ba.TRFSolver(prob, g["theta0"], ftol=1e-10, xtol=1e-12, gtol=1e-12, max_nfev=25, speculative=spec)
+        while not sol.done():
+            sol.iterate()
+        hist.append((sol.history, sol.x.cpu().numpy().copy(), sol.nfev))
+    (h0, x0, n0), (h1, x1, n1) = hist
+    assert n0 == n1 and len(h0) == len(h1)
+    for a, b in zip(h0, h1):
+        assert abs(a["alpha"] - b["alpha"]) <= 1e-9 * abs(a["alpha"])
+        assert abs(a["cost_new"] - b["cost_new"]) <= 1e-12 * abs(a["cost_new"])
+    assert np.max(np.abs(x0 - x1)) <= 1e-9 * np.max(np.abs(x0))
+
+
+def test_rejected_step_restores_linearisation(golden_dir):
+    """A deliberately rejected trial (pop) leaves the damped solve of the old linearisation unchanged."""
+    g, args, prob = _load(golden_dir, "partial")
+    th = prob._dev_theta(g["theta0"])
+    cost, ginf, g2, xn = prob.linearize(th)
+    alpha = 0.01 * g2 / xn
+    prob.trial(alpha, True)
+    p0 = prob.step.clone()
+    bad = th + 50.0 * torch.randn_like(th)             # a point far away: certainly a worse cost
+    prob.linearize_push()
+    cost_bad = prob.linearize(bad)[0]
+    assert cost_bad > cost
+    prob.linearize_pop()
+    prob.trial(alpha, True)
+    assert torch.equal(prob.step, p0)
+
+
+@pytest.mark.parametrize("C,N", [(9, 60), (11, 40), (16, 30), (33, 20)])
+def test_damped_step_many_cameras(C, N):
+    """Reduced systems of 54..198 unknowns: DMMA SYRK tiles with the trailing rows fused into diagonal tiles (one and
+    several tile rows) and the cooperative multi-CTA reduced solve, against a dense solve of the oracle's normal
+    equations."""
+    sc = scene.make_scene(C=C, N=N, seed=300 + C, score_mode="uniform", p_drop_2d=0.2, p_drop_3d=0.1)
+    sp2d, ss2d, sp3d, ss3d = scene.ba_inputs(sc)
+    J = ss2d.shape[2]
+    prob = ba.BAProblem(sc.K, sp2d, ss2d, sp3d, ss3d, ba.OP_BONE, 2.0, 30.0)
+    x0 = prob.triangulate(sc.R_init, sc.t_init)
+    th = ba.to_theta(sc.R_init, sc.t_init, x0.reshape(-1, 3))
+    args = (sc.K, sp2d.reshape(C, N * J, 2), ss2d, sp3d, ss3d, bo.OP_BONE, C, N, J, 2.0, 30.0)
+    f = bo.objfun(th, *args)
+    Jd = bo.jacobian(th, *args).toarray()
+    cost, ginf, g2, xn = prob.linearize(th)
+    grad = Jd.T @ f
+    assert abs(g2 - np.linalg.norm(grad)) <= 1e-9 * g2
+    for alpha in (1e-3 * g2 / xn, 1e-7 * g2 / xn):
+        pn2, gp, ptq = prob.trial(alpha, True)
+        A = Jd.T @ Jd + alpha * np.eye(Jd.shape[1])
+        p = np.linalg.solve(A, -grad)
+        pg = prob.step.cpu().numpy()
+        assert np.linalg.norm(pg - p) <= 1e-8 * np.linalg.norm(p)
+        assert abs(ptq - p @ np.linalg.solve(A, p)) <= 1e-7 * abs(ptq)
+
+
+def test_single_cta_and_cooperative_reduced_solve_agree(monkeypatch):
+    """BAX_DENSE_COOP=0 selects the single-CTA Cholesky; both must give the same step."""
+    sc = scene.make_scene(C=12, N=40, seed=77, score_mode="uniform", p_drop_2d=0.2, p_drop_3d=0.1)
+    sp2d, ss2d, sp3d, ss3d = scene.ba_inputs(sc)
+    steps = []
+    for flag in ("0", "1"):
+        monkeypatch.setenv("BAX_DENSE_COOP", flag)
+        prob = ba.BAProblem(sc.K, sp2d, ss2d, sp3d, ss3d, ba.OP_BONE, 1.0, 10.0)
+        x0 = prob.triangulate(sc.R_init, sc.t_init)
+        th = ba.to_theta(sc.R_init, sc.t_init, x0.reshape(-1, 3))
+        cost, ginf, g2, xn = prob.linearize(th)
+        prob.trial(1e-4 * g2 / xn, True)
+        steps.append(prob.step.cpu().numpy().copy())
+        prob.close()
+    assert np.linalg.norm(steps[0] - steps[1]) <= 1e-9 * np.linalg.norm(steps[0])
+
+
+def test_observation_rebind(golden_dir):
+    """bax_observations_rebind: a second device copy of the observations gives bit-identical residuals."""
+    g, args, prob = _load(golden_dir, "partial")
+    r0 = prob.residual(g["theta0"]).clone()
+    y2, s2 = prob.y.clone(), prob.s.clone()
+    prob.rebind_observations(y2, s2)
+    assert torch.equal(prob.residual(g["theta0"]), r0)
+
+
+@pytest.mark.parametrize("variant", ["0", "1", "2", "3"])
+def test_rj_kernel_variants_agree(monkeypatch, variant):
+    """Every store strategy of the fused residual + Jacobian kernel (LSU-staged and the TMA bulk-store variants)
+    returns the same blocks as the default one, ragged visibility included."""
+    sc = scene.make_scene(C=5, N=37, seed=41, score_mode="uniform", p_drop_2d=0.35, p_drop_3d=0.1)
+    sp2d, ss2d, sp3d, ss3d = scene.ba_inputs(sc)
+    outs = []
+    for v in (None, variant):
+        if v is None:
+            monkeypatch.delenv("BAX_RJ_VARIANT", raising=False)
+        else:
+            monkeypatch.setenv("BAX_RJ_VARIANT", v)
+        prob = ba.BAProblem(sc.K, sp2d, ss2d, sp3d, ss3d, ba.OP_BONE, 1.0, 1.0)
+        x0 = prob.triangulate(sc.R_init, sc.t_init)
+        th = ba.to_theta(sc.R_init, sc.t_init, x0.reshape(-1, 3))
+        outs.append([t.cpu().numpy().copy() for t in prob.residual_jacobian(th)])
+        prob.close()
+    for a, b in zip(*outs):
+        assert np.array_equal(a, b)
