@@ -48,7 +48,7 @@ k_rsx_fit_warp(int C, int64_t N, int64_t M, const double* __restrict__ v, const 
   }
 }
 
-__global__ void __launch_bounds__(SCORE_THREADS)
+__global__ void __launch_bounds__(SCORE_THREADS, 3)
 k_rsx_score(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
             const double* __restrict__ Rt, int64_t H, double* __restrict__ score, double* __restrict__ parts) {
   extern __shared__ __align__(16) double sm[];       // [C][12] model, then 2*32 reduction scratch
@@ -128,6 +128,10 @@ extern "C" int rsx_create(int device, rsx_handle** out) {
   BAX_CUDA(cudaMallocHost((void**)&h->host_pinned, 64 * sizeof(double)));
   h->red_bytes = sizeof(double) * (1 << 20);
   BAX_CUDA(cudaMalloc(&h->red, h->red_bytes));
+  {  // keep freed scratch of the final fit in the device pool instead of returning it to the driver at every sync
+    cudaMemPool_t pool; unsigned long long keep = ~0ULL;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+  }
   { const char* e = getenv("RSX_FIT_MODE"); h->fit_mode = e ? atoi(e) : 1; }   // 0: CTA Jacobi kernel only
   BAX_CUDA(cudaMalloc(&h->fit_stats, 2 * sizeof(unsigned long long)));
   BAX_CUDA(cudaMemset(h->fit_stats, 0, 2 * sizeof(unsigned long long)));

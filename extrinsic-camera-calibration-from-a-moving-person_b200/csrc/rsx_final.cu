@@ -347,11 +347,13 @@ __global__ void k_scale_X(double* __restrict__ X, int64_t n3, double f) {
 
 // ------------------------------------------------------------------ host driver
 namespace {
-struct DevBuf {
+struct DevBuf {               // stream-ordered scratch from the device's memory pool (no device-wide sync on release)
   void* p = nullptr;
-  ~DevBuf() { if (p) cudaFree(p); }
+  cudaStream_t st = 0;
+  ~DevBuf() { if (p) cudaFreeAsync(p, st); }
   cudaError_t alloc(size_t bytes, bool zero, cudaStream_t s) {
-    cudaError_t e = cudaMalloc(&p, bytes ? bytes : 8);
+    st = s;
+    cudaError_t e = cudaMallocAsync(&p, bytes ? bytes : 8, s);
     if (e == cudaSuccess && zero) e = cudaMemsetAsync(p, 0, bytes ? bytes : 8, s);
     return e;
   }

@@ -290,7 +290,9 @@ __host__ __device__ inline double score_points(const G& g, int C, int64_t M, con
       const double x0 = P[0] * X[0] + P[1] * X[1] + P[2] * X[2] + P[3] * X[3];
       const double x1 = P[4] * X[0] + P[5] * X[1] + P[6] * X[2] + P[7] * X[3];
       const double x2 = P[8] * X[0] + P[9] * X[1] + P[10] * X[2] + P[11] * X[3];
-      const double e0 = x0 / x2 - nn[0], e1 = x1 / x2 - nn[1], e2 = x2 / x2 - nn[2];
+      // one reciprocal instead of the reference's three divisions (calib_ransac.py:163-165); x2 / x2 is 1 or NaN
+      const double ix2 = 1.0 / x2;
+      const double e0 = x0 * ix2 - nn[0], e1 = x1 * ix2 - nn[1], e2 = ((x2 - x2) == 0.0 && x2 != 0.0 ? 1.0 : x2 * ix2) - nn[2];
       acc += e0 * e0 + e1 * e1 + e2 * e2;
       if (e_out) { double* o = e_out + ((size_t)i * C + c) * 3; o[0] = e0; o[1] = e1; o[2] = e2; }
       if (mask2d) inl = inl && (K00[c] * sqrt(e0 * e0 + e1 * e1) <= th2d);
