@@ -89,6 +89,51 @@ k_rj(const double* __restrict__ campack, const double* __restrict__ x, const dou
   for (int i = lane; i < 3 * nw; i += 32) jq[i] = stage[warp][(i / 3) * 9 + 6 + (i % 3)];
 }
 
+// Residual and Jacobian blocks of one observation, parked in shared memory in their final global layout as soon as
+// each exists (same arithmetic as obs_linearize<true>; keeps the live set near 18 doubles).
+__device__ __forceinline__ void rj_park(const double* cam, const double x0, const double x1, const double x2,
+                                        const double2 yy, const double sc, double2* stRk, double2* b, double2* aout) {
+  const double* K = cam; const double* R = cam + 9; const double* t = cam + 18; const double* M = cam + 21;
+  double jt[2][3];
+  {
+    const double P0 = R[0] * x0 + R[1] * x1 + R[2] * x2 + t[0];
+    const double P1 = R[3] * x0 + R[4] * x1 + R[5] * x2 + t[1];
+    const double P2 = R[6] * x0 + R[7] * x1 + R[8] * x2 + t[2];
+    const double q0 = K[0] * P0 + K[1] * P1 + K[2] * P2;
+    const double q1 = K[3] * P0 + K[4] * P1 + K[5] * P2;
+    const double q2 = K[6] * P0 + K[7] * P1 + K[8] * P2;
+    const double w = 1.4142135623730951 * sc;
+    const double yh0 = q0 / q2, yh1 = q1 / q2;
+    *stRk = make_double2((yy.x - yh0) * w, (yy.y - yh1) * w);
+    const double f = -w / q2;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      jt[0][k] = f * (K[k] - yh0 * K[6 + k]);
+      jt[1][k] = f * (K[3 + k] - yh1 * K[6 + k]);
+    }
+  }
+  double jp[2][3];
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) jp[a][k] = jt[a][0] * R[k] + jt[a][1] * R[3 + k] + jt[a][2] * R[6 + k];
+  b[0] = make_double2(jp[0][0], jp[0][1]);
+  b[1] = make_double2(jp[0][2], jp[1][0]);
+  b[2] = make_double2(jp[1][1], jp[1][2]);
+#pragma unroll
+  for (int a = 0; a < 2; ++a) {
+    const double c0 = x1 * jp[a][2] - x2 * jp[a][1];
+    const double c1 = x2 * jp[a][0] - x0 * jp[a][2];
+    const double c2 = x0 * jp[a][1] - x1 * jp[a][0];
+    const double r0 = c0 * M[0] + c1 * M[3] + c2 * M[6];
+    const double r1 = c0 * M[1] + c1 * M[4] + c2 * M[7];
+    const double r2v = c0 * M[2] + c1 * M[5] + c2 * M[8];
+    aout[3 * a + 0] = make_double2(r0, r1);
+    aout[3 * a + 1] = make_double2(r2v, jt[a][0]);
+    aout[3 * a + 2] = make_double2(jt[a][1], jt[a][2]);
+  }
+}
+
 // Bulk-store variant: the whole CTA stages its compacted rows in shared memory in their final global layout
 // (the rows of one CTA are contiguous in r2 / Jcam / Jpt), then three elected threads hand the three runs to the
 // TMA engine (cp.async.bulk shared::cta -> global).  The LSU issues no global stores for the Jacobian blocks, the
@@ -143,50 +188,7 @@ k_rj_bulk(const double* __restrict__ campack, const double* __restrict__ x, cons
   if (vis) {
     const int rk = wbase + wr;
     if (obs_cam) { obs_cam[row0 + rk] = c; obs_pt[row0 + rk] = (int32_t)p; }
-    // same arithmetic as obs_linearize<true>, ordered so that every block is parked in shared memory as soon as
-    // it exists (keeps the live set near 18 doubles)
-    const double* K = cam; const double* R = cam + 9; const double* t = cam + 18; const double* M = cam + 21;
-    const double x0 = x[3 * p], x1 = x[3 * p + 1], x2 = x[3 * p + 2];
-    double jt[2][3];
-    {
-      const double P0 = R[0] * x0 + R[1] * x1 + R[2] * x2 + t[0];
-      const double P1 = R[3] * x0 + R[4] * x1 + R[5] * x2 + t[1];
-      const double P2 = R[6] * x0 + R[7] * x1 + R[8] * x2 + t[2];
-      const double q0 = K[0] * P0 + K[1] * P1 + K[2] * P2;
-      const double q1 = K[3] * P0 + K[4] * P1 + K[5] * P2;
-      const double q2 = K[6] * P0 + K[7] * P1 + K[8] * P2;
-      const double w = 1.4142135623730951 * sc;
-      const double yh0 = q0 / q2, yh1 = q1 / q2;
-      stR[rk] = make_double2((yy.x - yh0) * w, (yy.y - yh1) * w);
-      const double f = -w / q2;
-#pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        jt[0][k] = f * (K[k] - yh0 * K[6 + k]);
-        jt[1][k] = f * (K[3 + k] - yh1 * K[6 + k]);
-      }
-    }
-    double jp[2][3];
-#pragma unroll
-    for (int a = 0; a < 2; ++a)
-#pragma unroll
-      for (int k = 0; k < 3; ++k) jp[a][k] = jt[a][0] * R[k] + jt[a][1] * R[3 + k] + jt[a][2] * R[6 + k];
-    double2* b = stJp + rk * 3;
-    b[0] = make_double2(jp[0][0], jp[0][1]);
-    b[1] = make_double2(jp[0][2], jp[1][0]);
-    b[2] = make_double2(jp[1][1], jp[1][2]);
-    double2* aout = stJc + rk * 6;
-#pragma unroll
-    for (int a = 0; a < 2; ++a) {
-      const double c0 = x1 * jp[a][2] - x2 * jp[a][1];
-      const double c1 = x2 * jp[a][0] - x0 * jp[a][2];
-      const double c2 = x0 * jp[a][1] - x1 * jp[a][0];
-      const double r0 = c0 * M[0] + c1 * M[3] + c2 * M[6];
-      const double r1 = c0 * M[1] + c1 * M[4] + c2 * M[7];
-      const double r2v = c0 * M[2] + c1 * M[5] + c2 * M[8];
-      aout[3 * a + 0] = make_double2(r0, r1);
-      aout[3 * a + 1] = make_double2(r2v, jt[a][0]);
-      aout[3 * a + 2] = make_double2(jt[a][1], jt[a][2]);
-    }
+    rj_park(cam, x[3 * p], x[3 * p + 1], x[3 * p + 2], yy, sc, stR + rk, stJp + rk * 3, stJc + rk * 6);
     asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");   // generic-proxy writes -> visible to the async proxy
   }
   __syncthreads();
@@ -194,6 +196,129 @@ k_rj_bulk(const double* __restrict__ campack, const double* __restrict__ x, cons
   if (threadIdx.x == 0) bulk_store_s2g(Jcam + row0 * 6, stJc, (unsigned)ntot * 96u);
   else if (threadIdx.x == 32) bulk_store_s2g(Jpt + row0 * 3, stJp, (unsigned)ntot * 48u);
   else if (threadIdx.x == 64) bulk_store_s2g(r2 + row0, stR, (unsigned)ntot * 16u);
+}
+
+
+// Persistent, TMA-pipelined variant (BAX_RJ_VARIANT=4).  One CTA per SM slot walks the (camera, 256-observation)
+// tiles with a fixed stride.  Every tile's inputs — 256 x (u,v) 4 KB, 256 x point 6 KB, 256 x score 2 KB and the
+// camera pack 384 B, all contiguous in HBM — arrive by four cp.async.bulk copies that complete on an mbarrier, into
+// a ring of STAGES shared-memory slots, so the loads of tile k+STAGES are in flight while tile k is computed and
+// its compacted rows leave through the bulk-store path of k_rj_bulk.  No thread ever waits on a global load.
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+  asm volatile(
+      "{\n.reg .pred p;\nWAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_load_g2s(void* sdst, const void* gsrc, unsigned bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
+               ::"r"(smem_u32(sdst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+constexpr int RJ_TILE = 256;
+constexpr int RJ_IN_Y = 0, RJ_IN_X = RJ_TILE * 16, RJ_IN_S = RJ_IN_X + RJ_TILE * 24, RJ_IN_CAM = RJ_IN_S + RJ_TILE * 8;
+constexpr int RJ_IN_BYTES = RJ_IN_CAM + CAMPACK * 8;      // 12 672 B per stage (a multiple of 128)
+constexpr int RJ_OUT_BYTES = RJ_TILE * 160;
+__host__ __device__ constexpr int rj_pipe_smem(int stages) { return RJ_OUT_BYTES + stages * RJ_IN_BYTES; }
+
+template <int STAGES, int MINB>
+__global__ void __launch_bounds__(RJ_TILE, MINB)
+k_rj_pipe(const double* __restrict__ campack, const double* __restrict__ x, const double2* __restrict__ y,
+          const double* __restrict__ s, int64_t P, const int64_t* __restrict__ blockbase, int nblk, int64_t ntiles,
+          double2* __restrict__ r2, double2* __restrict__ Jcam, double2* __restrict__ Jpt,
+          int32_t* __restrict__ obs_cam, int32_t* __restrict__ obs_pt) {
+  extern __shared__ __align__(128) unsigned char smraw[];
+  double2* stJc = reinterpret_cast<double2*>(smraw);          // [256][6]
+  double2* stJp = stJc + RJ_TILE * 6;                         // [256][3]
+  double2* stR = stJp + RJ_TILE * 3;                          // [256]
+  unsigned char* ring = smraw + RJ_OUT_BYTES;
+  __shared__ __align__(8) uint64_t full[STAGES];
+  __shared__ int s_warp[RJ_TILE / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+  auto issue_loads = [&](int64_t t, int stage) {              // thread 0 only
+    const int c = (int)(t / nblk);
+    const int64_t p0 = (t - (int64_t)c * nblk) * RJ_TILE;
+    const int64_t rem = P - p0;
+    const unsigned cnt = rem < RJ_TILE ? (unsigned)rem : (unsigned)RJ_TILE;   // even: P is even on this path
+    unsigned char* st = ring + (size_t)stage * RJ_IN_BYTES;
+    mbar_expect_tx(&full[stage], cnt * 48u + CAMPACK * 8u);
+    bulk_load_g2s(st + RJ_IN_Y, y + (size_t)c * P + p0, cnt * 16u, &full[stage]);
+    bulk_load_g2s(st + RJ_IN_X, x + 3 * p0, cnt * 24u, &full[stage]);
+    bulk_load_g2s(st + RJ_IN_S, s + (size_t)c * P + p0, cnt * 8u, &full[stage]);
+    bulk_load_g2s(st + RJ_IN_CAM, campack + (size_t)c * CAMPACK, CAMPACK * 8u, &full[stage]);
+  };
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int i = 0; i < STAGES; ++i) mbar_init(&full[i], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int i = 0; i < STAGES; ++i) {
+      const int64_t t = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
+      if (t < ntiles) issue_loads(t, i);
+    }
+  }
+  int stage = 0; unsigned parity = 0;
+  int64_t row0 = blockIdx.x < ntiles ? blockbase[blockIdx.x] : 0;      // [C][nblk] is tile-indexed
+  for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const int64_t tnext = t + gridDim.x;
+    const int64_t row0_next = tnext < ntiles ? blockbase[tnext] : 0;    // in flight under this tile's arithmetic
+    const int c = (int)(t / nblk);
+    const int blk = (int)(t - (int64_t)c * nblk);
+    const int64_t p = (int64_t)blk * RJ_TILE + threadIdx.x;
+    const unsigned char* st = ring + (size_t)stage * RJ_IN_BYTES;
+    mbar_wait(&full[stage], parity);
+    double sc = 0.0; double2 yy = make_double2(0, 0); double x0 = 0, x1 = 0, x2 = 0;
+    if (p < P) {
+      sc = reinterpret_cast<const double*>(st + RJ_IN_S)[threadIdx.x];
+      yy = reinterpret_cast<const double2*>(st + RJ_IN_Y)[threadIdx.x];
+      const double* xs = reinterpret_cast<const double*>(st + RJ_IN_X) + 3 * threadIdx.x;
+      x0 = xs[0]; x1 = xs[1]; x2 = xs[2];
+    }
+    const double* cam = reinterpret_cast<const double*>(st + RJ_IN_CAM);
+    const bool vis = sc > 0;
+    const unsigned bal = __ballot_sync(0xffffffffu, vis);
+    const int wr = __popc(bal & ((1u << lane) - 1u));
+    if (lane == 0) s_warp[warp] = __popc(bal);
+    // the staging area is free once the TMA engine has read the previous tile's rows out of it
+    if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");
+    __syncthreads();
+    int wbase = 0, ntot = 0;
+#pragma unroll
+    for (int w = 0; w < RJ_TILE / 32; ++w) { const int v = s_warp[w]; wbase += (w < warp) ? v : 0; ntot += v; }
+    if (vis) {
+      const int rk = wbase + wr;
+      if (obs_cam) { obs_cam[row0 + rk] = c; obs_pt[row0 + rk] = (int32_t)p; }
+      rj_park(cam, x0, x1, x2, yy, sc, stR + rk, stJp + rk * 3, stJc + rk * 6);
+      asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+    }
+    __syncthreads();                       // rows parked; every thread is done with this input slot and s_warp
+    if (threadIdx.x == 0) {
+      if (ntot > 0) {
+        const unsigned n = (unsigned)ntot;
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n" ::"l"(Jcam + row0 * 6), "r"(smem_u32(stJc)), "r"(n * 96u) : "memory");
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n" ::"l"(Jpt + row0 * 3), "r"(smem_u32(stJp)), "r"(n * 48u) : "memory");
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n" ::"l"(r2 + row0), "r"(smem_u32(stR)), "r"(n * 16u) : "memory");
+        asm volatile("cp.async.bulk.commit_group;\n" ::: "memory");
+      }
+      const int64_t tn = t + (int64_t)STAGES * gridDim.x;
+      if (tn < ntiles) issue_loads(tn, stage);
+    }
+    if (++stage == STAGES) { stage = 0; parity ^= 1u; }
+    row0 = row0_next;
+  }
+  if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");   // smem must outlive the last reads
 }
 
 // ------------------------------------------------------------------ orientation rows  (ba.py:67-96)
@@ -323,6 +448,29 @@ extern "C" int bax_residual_jacobian(bax_handle* h, const double* theta, double*
         k_rj<<<dim3(h->nblk_obs, h->C), 256, 0, s>>>(RJ_ARGS, RJ_OUT);
         break;
       case 2: {
+        const int smem = 128 * 160;
+        k_rj_bulk<128, 8><<<dim3(h->nblk_obs * 2, h->C), 128, smem, s>>>(RJ_ARGS, 2, RJ_OUT);
+        break;
+      }
+      case 4: case 5: {
+        // persistent TMA pipeline; its bulk loads need 16-byte aligned score rows (P even), else variant 2
+        if ((h->P & 1) == 0 && (((uintptr_t)x | (uintptr_t)h->y2d | (uintptr_t)h->s2d) & 15) == 0) {
+          const int64_t ntiles = (int64_t)h->nblk_obs * h->C;
+          if (h->rj_variant == 4) {
+            constexpr int smem = rj_pipe_smem(2);
+            static bool once = false;
+            if (!once) { BAX_CUDA(cudaFuncSetAttribute(k_rj_pipe<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); once = true; }
+            int64_t g = (int64_t)h->sm_count * 3; if (g > ntiles) g = ntiles;
+            k_rj_pipe<2, 3><<<(unsigned)g, RJ_TILE, smem, s>>>(RJ_ARGS, h->nblk_obs, ntiles, RJ_OUT);
+          } else {
+            constexpr int smem = rj_pipe_smem(4);
+            static bool once = false;
+            if (!once) { BAX_CUDA(cudaFuncSetAttribute(k_rj_pipe<4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); once = true; }
+            int64_t g = (int64_t)h->sm_count * 2; if (g > ntiles) g = ntiles;
+            k_rj_pipe<4, 2><<<(unsigned)g, RJ_TILE, smem, s>>>(RJ_ARGS, h->nblk_obs, ntiles, RJ_OUT);
+          }
+          break;
+        }
         const int smem = 128 * 160;
         k_rj_bulk<128, 8><<<dim3(h->nblk_obs * 2, h->C), 128, smem, s>>>(RJ_ARGS, 2, RJ_OUT);
         break;
