@@ -76,7 +76,7 @@ struct bax_handle {
   double* host_pinned;       // small pinned staging for scalars
   // ---- timing
   int dense_coop;            // 1: cooperative multi-CTA reduced solve (env BAX_DENSE_COOP=0 selects the single-CTA kernel)
-  int rj_variant;            // tuning knob (env BAX_RJ_VARIANT): 0 = per-warp staged LSU stores; 1/2/3 = CTA-staged TMA bulk stores (256x4, 128x8 [default], 256x3)
+  int rj_variant;            // tuning knob (env BAX_RJ_VARIANT): -1 = auto [default: 5 or 4]; 0 = per-warp staged LSU stores; 1/2/3 = CTA-staged TMA bulk stores (256x4, 128x8, 256x3); 4..8 = persistent TMA pipeline (stages x CTAs/SM: 2x3, 4x2, 3x2, 5x2, 8x1)
   int timing;
   cudaEvent_t ev0, ev1;
   double t_ms[BAX_T_COUNT];

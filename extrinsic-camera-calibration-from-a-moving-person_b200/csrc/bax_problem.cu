@@ -144,7 +144,7 @@ extern "C" int bax_create(int device, bax_handle** out) {
   BAX_CUDA(cudaGetDeviceProperties(&prop, device));
   h->sm_count = prop.multiProcessorCount;
   { const char* e = getenv("BAX_DENSE_COOP"); h->dense_coop = e ? atoi(e) : 1; }
-  { const char* e = getenv("BAX_RJ_VARIANT"); h->rj_variant = e ? atoi(e) : 2; }
+  { const char* e = getenv("BAX_RJ_VARIANT"); h->rj_variant = e ? atoi(e) : -1; }
   BAX_CUDA(cudaEventCreate(&h->ev0));
   BAX_CUDA(cudaEventCreate(&h->ev1));
   BAX_CUDA(cudaMallocHost((void**)&h->host_pinned, 64 * sizeof(double)));

@@ -443,7 +443,11 @@ extern "C" int bax_residual_jacobian(bax_handle* h, const double* theta, double*
     const double* x = theta + 6 * h->C;
 #define RJ_ARGS h->campack, x, (const double2*)h->y2d, h->s2d, h->P, h->blockbase
 #define RJ_OUT (double2*)r2, (double2*)Jcam, (double2*)Jpt, obs_cam, obs_pt
-    switch (h->rj_variant) {
+    // default (BAX_RJ_VARIANT unset): the persistent TMA pipeline, 2 CTAs/SM x 4 input stages when (nearly) every
+    // observation is visible, 3 CTAs/SM x 2 stages when compaction leaves threads idle (more warps hide the arithmetic)
+    int variant = h->rj_variant;
+    if (variant < 0) variant = (double)h->n_vis >= 0.9 * (double)h->C * (double)h->P ? 5 : 4;
+    switch (variant) {
       case 0:
         k_rj<<<dim3(h->nblk_obs, h->C), 256, 0, s>>>(RJ_ARGS, RJ_OUT);
         break;
@@ -452,23 +456,26 @@ extern "C" int bax_residual_jacobian(bax_handle* h, const double* theta, double*
         k_rj_bulk<128, 8><<<dim3(h->nblk_obs * 2, h->C), 128, smem, s>>>(RJ_ARGS, 2, RJ_OUT);
         break;
       }
-      case 4: case 5: {
+      case 4: case 5: case 6: case 7: case 8: {
         // persistent TMA pipeline; its bulk loads need 16-byte aligned score rows (P even), else variant 2
         if ((h->P & 1) == 0 && (((uintptr_t)x | (uintptr_t)h->y2d | (uintptr_t)h->s2d) & 15) == 0) {
           const int64_t ntiles = (int64_t)h->nblk_obs * h->C;
-          if (h->rj_variant == 4) {
-            constexpr int smem = rj_pipe_smem(2);
-            static bool once = false;
-            if (!once) { BAX_CUDA(cudaFuncSetAttribute(k_rj_pipe<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); once = true; }
-            int64_t g = (int64_t)h->sm_count * 3; if (g > ntiles) g = ntiles;
-            k_rj_pipe<2, 3><<<(unsigned)g, RJ_TILE, smem, s>>>(RJ_ARGS, h->nblk_obs, ntiles, RJ_OUT);
-          } else {
-            constexpr int smem = rj_pipe_smem(4);
-            static bool once = false;
-            if (!once) { BAX_CUDA(cudaFuncSetAttribute(k_rj_pipe<4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); once = true; }
-            int64_t g = (int64_t)h->sm_count * 2; if (g > ntiles) g = ntiles;
-            k_rj_pipe<4, 2><<<(unsigned)g, RJ_TILE, smem, s>>>(RJ_ARGS, h->nblk_obs, ntiles, RJ_OUT);
+#define RJ_PIPE(ST, MB)                                                                                              \
+  {                                                                                                                  \
+    constexpr int smem = rj_pipe_smem(ST);                                                                           \
+    static bool once = false;                                                                                        \
+    if (!once) { BAX_CUDA(cudaFuncSetAttribute(k_rj_pipe<ST, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); once = true; } \
+    int64_t g = (int64_t)h->sm_count * MB; if (g > ntiles) g = ntiles;                                               \
+    k_rj_pipe<ST, MB><<<(unsigned)g, RJ_TILE, smem, s>>>(RJ_ARGS, h->nblk_obs, ntiles, RJ_OUT);                      \
+  }
+          switch (variant) {
+            case 4: RJ_PIPE(2, 3) break;
+            case 6: RJ_PIPE(3, 2) break;
+            case 7: RJ_PIPE(5, 2) break;
+            case 8: RJ_PIPE(8, 1) break;
+            default: RJ_PIPE(4, 2) break;
           }
+#undef RJ_PIPE
           break;
         }
         const int smem = 128 * 160;

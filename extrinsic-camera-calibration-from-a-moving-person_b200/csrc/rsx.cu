@@ -29,7 +29,7 @@ k_rsx_fit(int C, int64_t N, int64_t M, const double* __restrict__ v, const doubl
 __global__ void __launch_bounds__(32 * FITW_WARPS)
 k_rsx_fit_warp(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
                const int32_t* __restrict__ samp_v, const int32_t* __restrict__ samp_m, int64_t H,
-               double* __restrict__ Rt, unsigned long long* __restrict__ stats /*[2]: fall-backs, sweeps*/) {
+               double* __restrict__ Rt, unsigned long long* __restrict__ stats /*[3]: fall-backs, sweeps, work counter*/) {
   extern __shared__ __align__(16) double sm[];
   const int nu = 3 * (RSX_S + C), ld = nu | 1;
   const size_t per_warp = (fit_ws_small_doubles(C) + 2 * (size_t)nu * ld + 1) & ~(size_t)1;
@@ -37,8 +37,13 @@ k_rsx_fit_warp(int C, int64_t N, int64_t M, const double* __restrict__ v, const 
   FitWs ws;
   fit_ws_carve(sm + warp * per_warp, nullptr, C, ws);
   WarpCtx g{lane, 32};
-  const int64_t stride = (int64_t)gridDim.x * FITW_WARPS;
-  for (int64_t h = (int64_t)blockIdx.x * FITW_WARPS + warp; h < H; h += stride) {
+  // hypotheses are handed out one at a time from a global counter: a fit's cost varies (sweep count, the rare Jacobi
+  // fall-back is ~50x a normal fit), so a fixed stride leaves most SMs idle while the slowest warp finishes
+  for (;;) {
+    long long h = 0;
+    if (lane == 0) h = (long long)atomicAdd(stats + 2, 1ULL);
+    h = __shfl_sync(0xffffffffu, h, 0);
+    if (h >= H) break;
     fit_hypothesis(g, C, N, M, v, n, samp_v + h * RSX_S, samp_m + h * RSX_S, ws, Rt + (size_t)h * C * 12, true);
     if (stats && lane == 0) {
       const int sw = ws.iflag[8];
@@ -107,6 +112,31 @@ k_rsx_masks(int C, int64_t N, int64_t M, const double* __restrict__ v, const dou
   score_dirs(g, C, N, v, sm, e3d_out, th3d, mask3d);
 }
 
+// DLT re-triangulation of every ray set under one model (calib_linear.py:127-133 -> pycalib.calib.triangulate ==
+// util.py:240-258): the eigenvector of the smallest eigenvalue of sum_c a^T a, dehomogenised unless
+// np.isclose(x[3], 0)  (|x3| <= 1e-8), in which case the unit eigenvector itself is returned.  One thread per point.
+__global__ void __launch_bounds__(256)
+k_rsx_triangulate(int C, int64_t M, const double* __restrict__ n, const double* __restrict__ Rt, double* __restrict__ X4) {
+  extern __shared__ __align__(16) double sm[];       // [C][12]
+  for (int i = threadIdx.x; i < 12 * C; i += blockDim.x) sm[i] = Rt[i];
+  __syncthreads();
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (int64_t)gridDim.x * blockDim.x) {
+    double m[10];
+#pragma unroll
+    for (int e = 0; e < 10; ++e) m[e] = 0.0;
+    for (int c = 0; c < C; ++c) {
+      const double* nn = n + ((size_t)c * M + i) * 3;
+      dlt_accumulate(sm + 12 * c, nn[0], nn[1], m);
+    }
+    double X[4];
+    eig4_smallest_fast(m, X);
+    const bool at_infinity = fabs(X[3]) <= 1e-8;     // np.isclose(v[3, 0], 0): atol 1e-8 (+ rtol * 0)
+    const double w = at_infinity ? 1.0 : X[3];
+    double* o = X4 + (size_t)i * 4;
+    o[0] = X[0] / w; o[1] = X[1] / w; o[2] = X[2] / w; o[3] = at_infinity ? X[3] : 1.0;
+  }
+}
+
 __global__ void k_rsx_count(const uint8_t* __restrict__ m, int64_t n, unsigned long long* __restrict__ out) {
   unsigned long long c = 0;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) c += m[i];
@@ -133,8 +163,8 @@ extern "C" int rsx_create(int device, rsx_handle** out) {
     if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
   }
   { const char* e = getenv("RSX_FIT_MODE"); h->fit_mode = e ? atoi(e) : 1; }   // 0: CTA Jacobi kernel only
-  BAX_CUDA(cudaMalloc(&h->fit_stats, 2 * sizeof(unsigned long long)));
-  BAX_CUDA(cudaMemset(h->fit_stats, 0, 2 * sizeof(unsigned long long)));
+  BAX_CUDA(cudaMalloc(&h->fit_stats, 4 * sizeof(unsigned long long)));
+  BAX_CUDA(cudaMemset(h->fit_stats, 0, 4 * sizeof(unsigned long long)));
   h->bx = (bax_handle*)calloc(1, sizeof(bax_handle));
   h->bx->device = device; h->bx->sm_count = h->sm_count;
   *out = h;
@@ -194,8 +224,9 @@ int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, 
     if (h->fit_mode != 0 && smem <= 110 * 1024 && arrow_ws_doubles(C, 32) <= (size_t)nu * ld) {
       const int per_sm = (int)((220 * 1024) / smem);
       int64_t grid = (H + FITW_WARPS - 1) / FITW_WARPS;
-      const int64_t cap = (int64_t)h->sm_count * per_sm * 4;
+      const int64_t cap = (int64_t)h->sm_count * per_sm;          // resident CTAs only: work is handed out dynamically
       if (grid > cap) grid = cap;
+      BAX_CUDA(cudaMemsetAsync((unsigned long long*)h->fit_stats + 2, 0, sizeof(unsigned long long), s));
       BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_warp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       RsxTimer t(h, RSX_T_FIT, s, 1);
       k_rsx_fit_warp<<<(unsigned)grid, 32 * FITW_WARPS, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt,
@@ -284,6 +315,17 @@ extern "C" int rsx_winner_masks(rsx_handle* h, const double* Rt, const double* K
   BAX_CUDA(cudaMemcpyAsync(hc, cnt, sizeof(hc), cudaMemcpyDeviceToHost, s));
   BAX_CUDA(cudaStreamSynchronize(s));
   if (counts_host) { counts_host[0] = (int64_t)hc[0]; counts_host[1] = (int64_t)hc[1]; }
+  return BAX_OK;
+}
+
+extern "C" int rsx_triangulate(rsx_handle* h, const double* Rt, double* X4_out, void* stream) {
+  if (!h || !h->n || !Rt || !X4_out) { bax_set_error("rsx_triangulate: bad argument / no problem"); return BAX_E_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  BAX_CUDA(cudaSetDevice(h->device));
+  int grid = (int)((h->M + 255) / 256); if (grid > 8 * h->sm_count) grid = 8 * h->sm_count;
+  RsxTimer t(h, RSX_T_OTHER, s, 1);
+  k_rsx_triangulate<<<grid, 256, sizeof(double) * 12 * h->C, s>>>(h->C, h->M, h->n, Rt, X4_out);
+  BAX_LAUNCH_CHECK();
   return BAX_OK;
 }
 

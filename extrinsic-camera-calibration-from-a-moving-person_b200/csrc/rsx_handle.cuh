@@ -15,7 +15,7 @@ struct rsx_handle {
   double* fit_scratch;  // global H/V workspace when 3(10+C) is too large for shared memory
   size_t fit_scratch_bytes;
   int fit_mode;         // 1: warp-per-hypothesis arrow solver where it fits (env RSX_FIT_MODE=0: CTA Jacobi kernel)
-  void* fit_stats;      // device [2] uint64: Jacobi fall-backs, total sweeps of the arrow solver
+  void* fit_stats;      // device [4] uint64: Jacobi fall-backs, total sweeps of the arrow solver, work counter of k_rsx_fit_warp
   double* red;          // small reduction scratch
   size_t red_bytes;
   double* host_pinned;  // [64]

@@ -64,6 +64,11 @@ int rsx_winner_masks(rsx_handle* h, const double* Rt, const double* K00, double 
 int rsx_calib_linear(rsx_handle* h, const uint8_t* mask3d, const uint8_t* mask2d, double* Rt_out, double* X_out,
                      int64_t* info_host, void* stream);
 
+/* DLT re-triangulation of all M ray sets under one model: calib_linear.py:127-133, i.e. pycalib.calib.triangulate
+ * (identical code vendored at util.py:240-258) per point.  Rt device [C][12]; X4_out device [M][4]: the
+ * dehomogenised point [x, y, z, 1], or the unit eigenvector itself where np.isclose(x[3], 0) (point at infinity). */
+int rsx_triangulate(rsx_handle* h, const double* Rt, double* X4_out, void* stream);
+
 /* timing hooks: CUDA-event ms and launch counts of { fit, score, final } since the last reset */
 int rsx_timing_enable(rsx_handle* h, int on);
 int rsx_timing_read(rsx_handle* h, double* ms_host /*[4]*/, int64_t* launches_host /*[4]*/);

@@ -165,8 +165,51 @@ def gen_cli(name="cli_c4"):
     print("wrote", name)
 
 
+def gen_linear(name="linear_c4"):
+    """File-level golden of the non-RANSAC linear calibration: the cli_c4 scene pushed through the reference's
+    own calib_linear.main_linear (calib_linear.py:138-215)."""
+    import tempfile
+    dataio = importlib.import_module("extrinsic-camera-calibration-from-a-moving-person_b200.dataio")
+    _, rc, ru = ref_shim.load()
+    from importlib import util as _iu
+    spec = _iu.spec_from_file_location("ref_calib_linear", os.path.join(ref_shim.REF, "calib_linear.py"))
+    rl = _iu.module_from_spec(spec)            # the reference's file, not this repo's drop-in of the same name
+    import types
+    sys.modules["util"] = ru                              # its `from util import *` / `from argument import ...`
+    pc = types.ModuleType("pycalib"); pc.calib = types.ModuleType("pycalib.calib")
+    pc.calib.triangulate = ru.triangulate                 # vendored identical copy, util.py:240-258
+    sys.modules["pycalib"], sys.modules["pycalib.calib"] = pc, pc.calib
+    sys.path.insert(0, ref_shim.REF)
+    argv, sys.argv = sys.argv, ["x"]
+    try:
+        spec.loader.exec_module(rl)
+    finally:
+        sys.argv = argv
+        sys.path.remove(ref_shim.REF)
+        for k in ("util", "argument", "pycalib", "pycalib.calib"):
+            sys.modules.pop(k, None)
+    kw = dict(C=4, N=24, seed=31, p_drop_2d=0.1, p_drop_3d=0.05)
+    sc = scene_mod.make_scene(**kw)
+    aid, pid, gid, frame_skip = 23, 102, 3, 2
+    with tempfile.TemporaryDirectory() as tmp:
+        d = os.path.join(tmp, "noise_3_0")
+        dataio.write_scene(d, sc, aid, pid, gid)
+        loaded = ru.load_eldersim(d, gid, aid, pid)
+        with quiet(), contextlib.redirect_stderr(io.StringIO()):
+            R, t, X, e, camid, K = rl.main_linear(d, gid, aid, pid, ru.OP_BONE, ru.OP_KEY_SUB, False,
+                                                  frame_skip=frame_skip)
+    np.savez_compressed(os.path.join(OUT, f"{name}.npz"), scene_kw=str(kw), aid=aid, pid=pid, gid=gid,
+                        frame_skip=frame_skip, R_linear=R, t_linear=t, X_linear=X, e_linear=e, CAMID=camid, K=K,
+                        p3d=loaded[5], s3d=loaded[6], p2d=loaded[7], s2d=loaded[8], frames=loaded[9],
+                        versions=str(versions()))
+    print("wrote", name)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if len(sys.argv) > 1 and sys.argv[1] == "linear":
+        gen_linear()
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "cli":
         gen_cli()
         return
@@ -179,6 +222,7 @@ def main():
     gen_ransac("c4", dict(C=4, N=40, seed=21, p_drop_2d=0.1, p_drop_3d=0.05), 12, 0, 50.0, 5.0)
     gen_ransac("c3", dict(C=3, N=30, seed=22, sigma_px=1.0), 8, 7, 50.0, 5.0)
     gen_cli()
+    gen_linear()
 
 
 if __name__ == "__main__":

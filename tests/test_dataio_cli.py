@@ -101,3 +101,30 @@ def test_cli_chain_ransac_then_ba(golden_dir, tmp_path):
     masked = os.path.join(prefix, "noise_3_0", "2d_joint_mask", dataio.joint_file(23, 102, 3, 21))
     fr, pose, score = dataio.load_poses(masked)
     assert len(fr) == sc.N and pose.shape == (sc.N, 50) and score.shape == (sc.N, 25)
+
+
+@pytest.mark.gpu
+def test_calib_linear_dropin_vs_reference_golden(golden_dir, tmp_path):
+    """calib_linear.sh / calib_linear.main_linear on the files the reference's own main_linear read
+    (oracle/gen_golden.py gen_linear): cameras 1e-9, re-triangulated points 1e-8 relative, its reprojection figure."""
+    g = np.load(os.path.join(golden_dir, "linear_c4.npz"))
+    sc = scene.make_scene(**ast.literal_eval(str(g["scene_kw"])))
+    prefix = str(tmp_path / "A023_P102_G003")
+    dataio.write_scene(os.path.join(prefix, "noise_3_0"), sc, 23, 102, 3)
+    from calib_b200 import calib_linear as cl
+    from calib_b200.ba import OP_BONE
+    R, t, X, e, camid, K = cl.main_linear(os.path.join(prefix, "noise_3_0"), 3, 23, 102, OP_BONE, None, False,
+                                          frame_skip=int(g["frame_skip"]))
+    assert np.array_equal(camid, g["CAMID"]) and np.array_equal(K, g["K"])
+    assert np.max(np.abs(R - g["R_linear"])) < 1e-9 and np.max(np.abs(t - g["t_linear"])) < 1e-9
+    assert X.shape == g["X_linear"].shape
+    assert np.max(np.abs(X - g["X_linear"])) < 1e-8 * np.max(np.abs(g["X_linear"]))
+    assert abs(e - float(g["e_linear"])) < 1e-8 * float(g["e_linear"])
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    out = subprocess.run(["bash", os.path.join(ROOT, "calib_linear.sh"), prefix, "23", "102", "3", "noise_3_0",
+                          str(int(g["frame_skip"])), "SynADL", "false"], cwd=ROOT, env=env, capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert "dataset=SynADL" in out.stdout and "vc=(4," in out.stdout
+    camid2, K2, R2, t2 = dataio.load_cameras(os.path.join(prefix, "results", "linear_3_0.json"))
+    assert np.array_equal(camid2, g["CAMID"]) and np.max(np.abs(R2 - g["R_linear"])) < 1e-9
+    assert np.max(np.abs(t2 - g["t_linear"])) < 1e-9
