@@ -44,6 +44,7 @@ _SIGS = {
     "bax_trial_mid": (i32, [vp, vp, i32, vp]),
     "bax_trial_finish": (i32, [vp, P_f64, vp]),
     "bax_triangulate": (i32, [vp, vp, vp, vp, P_i32, vp]),
+    "bax_reproject_error": (i32, [vp, vp, vp, vp, vp, vp]),
     "bax_timing_enable": (i32, [vp, i32]),
     "bax_timing_read": (i32, [vp, P_f64, P_i64]),
     "bax_timing_reset": (i32, [vp]),

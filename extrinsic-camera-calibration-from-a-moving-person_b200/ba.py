@@ -316,6 +316,19 @@ class BAProblem:
             raise Exception("not enough constraint")          # reference util.py:320-321
         return X.cpu().numpy().reshape(self.N, self.J, 3)
 
+    def reproject_error(self, R_w2c, t_w2c, X):
+        """Pixel distance between every observation and the projection of its point (eval.py:76-108, ba.py:248-256)
+        -> (C, N, J) numpy, NaN where invisible."""
+        f = dict(dtype=torch.float64, device=self.dev)
+        R = torch.as_tensor(np.asarray(R_w2c, dtype=np.float64)).to(**f).contiguous()
+        t = torch.as_tensor(np.asarray(t_w2c, dtype=np.float64).reshape(self.C, 3)).to(**f).contiguous()
+        Xd = torch.as_tensor(np.asarray(X, dtype=np.float64).reshape(self.P, 3)).to(**f).contiguous()
+        e = torch.empty(self.C, self.P, **f)
+        with torch.cuda.device(self.dev):
+            check(self.L.bax_reproject_error(self.h, R.data_ptr(), t.data_ptr(), Xd.data_ptr(), e.data_ptr(), _stream()),
+                  "bax_reproject_error")
+        return e.cpu().numpy().reshape(self.C, self.N, self.J)
+
     # ---- timing hooks
     def timing(self, on=True):
         check(self.L.bax_timing_enable(self.h, 1 if on else 0))

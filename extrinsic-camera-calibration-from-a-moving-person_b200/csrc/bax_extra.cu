@@ -90,6 +90,48 @@ extern "C" int bax_triangulate(bax_handle* h, const double* R, const double* t, 
   return BAX_OK;
 }
 
+// ---- reprojection error of every observation under given cameras and points (eval.calc_repro_error, eval.py:76-108;
+// also the distance test of ba.save_mask, ba.py:248-256): e[c][p] = || pi(K_c (R_c X_p + t_c)) - y_cp ||_2 in pixels,
+// NaN where the observation is invisible (score <= 0 or NaN) or the point is NaN.  One thread per (camera, point).
+__global__ void __launch_bounds__(256)
+k_reproject_error(const double* __restrict__ K, const double* __restrict__ R, const double* __restrict__ t,
+                  const double2* __restrict__ y, const double* __restrict__ sc, const double* __restrict__ X,
+                  int64_t P, double* __restrict__ e_out) {
+  __shared__ double cam[21];
+  const int c = blockIdx.y;
+  if (threadIdx.x < 9) { cam[threadIdx.x] = K[9 * c + threadIdx.x]; cam[9 + threadIdx.x] = R[9 * c + threadIdx.x]; }
+  if (threadIdx.x < 3) cam[18 + threadIdx.x] = t[3 * c + threadIdx.x];
+  __syncthreads();
+  const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  const double s = sc[(size_t)c * P + p];
+  double e = nan("");
+  if (s > 0) {
+    const double2 yy = y[(size_t)c * P + p];
+    const double x0 = X[3 * p], x1 = X[3 * p + 1], x2 = X[3 * p + 2];
+    const double* Km = cam; const double* Rm = cam + 9; const double* tm = cam + 18;
+    const double P0 = Rm[0] * x0 + Rm[1] * x1 + Rm[2] * x2 + tm[0];
+    const double P1 = Rm[3] * x0 + Rm[4] * x1 + Rm[5] * x2 + tm[1];
+    const double P2 = Rm[6] * x0 + Rm[7] * x1 + Rm[8] * x2 + tm[2];
+    const double q0 = Km[0] * P0 + Km[1] * P1 + Km[2] * P2;
+    const double q1 = Km[3] * P0 + Km[4] * P1 + Km[5] * P2;
+    const double q2 = Km[6] * P0 + Km[7] * P1 + Km[8] * P2;
+    const double d0 = q0 / q2 - yy.x, d1 = q1 / q2 - yy.y;
+    e = sqrt(d0 * d0 + d1 * d1);
+  }
+  e_out[(size_t)c * P + p] = e;
+}
+
+extern "C" int bax_reproject_error(bax_handle* h, const double* R, const double* t, const double* X, double* e_out,
+                                   void* stream) {
+  if (!h || !h->K || !R || !t || !X || !e_out) { bax_set_error("bax_reproject_error: bad argument / no problem"); return BAX_E_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  BAX_CUDA(cudaSetDevice(h->device));
+  k_reproject_error<<<dim3((unsigned)((h->P + 255) / 256), h->C), 256, 0, s>>>(h->K, R, t, (const double2*)h->y2d, h->s2d, X, h->P, e_out);
+  BAX_LAUNCH_CHECK();
+  return BAX_OK;
+}
+
 // ---- prior Jacobians for the public (SciPy-callback style) API
 __global__ void k_lbar(const double* __restrict__ bone_buf, int B, double* __restrict__ Lbar) {
   int b = threadIdx.x;

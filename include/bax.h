@@ -111,6 +111,11 @@ int bax_trial_finish(bax_handle* h, double* out_host, void* stream);
 int bax_triangulate(bax_handle* h, const double* R, const double* t, double* X, int32_t* status_host,
                     void* stream);
 
+/* Reprojection error in pixels of every observation under cameras (R [C][9], t [C][3]) and points X [N*J][3]:
+ * eval.calc_repro_error (reference eval.py:76-108) and the distance test of ba.save_mask (ba.py:248-256).
+ * e_out [C][N*J]; NaN where the observation is invisible or the point is NaN. */
+int bax_reproject_error(bax_handle* h, const double* R, const double* t, const double* X, double* e_out, void* stream);
+
 /* timing hooks for bench.py: CUDA-event time (ms) accumulated on the call's stream per kernel family */
 enum { BAX_T_RJ = 0, BAX_T_BUILD = 1, BAX_T_SYRK = 2, BAX_T_DENSE = 3, BAX_T_BACKSUB = 4, BAX_T_LIN = 5,
        BAX_T_COST = 6, BAX_T_COUNT = 8 };

@@ -205,8 +205,66 @@ def gen_linear(name="linear_c4"):
     print("wrote", name)
 
 
+def gen_eval(name="eval_c4"):
+    """Golden of the evaluation metrics: the reference's own eval.align / eval.calc_repro_error / util.eval_R /
+    util.eval_t / util.triangulate_with_conf, strung together as eval.eval_main does (eval.py:126-150), plus the
+    JSON summary eval_main writes.  pycalib.calib.absolute_orientation is not installable here: it is stubbed with
+    the restatement in calib_b200/eval.py, so THAT function is not pinned by this golden (everything around it is)."""
+    import tempfile
+    import types
+    from importlib import util as _iu
+    my_eval = importlib.import_module("extrinsic-camera-calibration-from-a-moving-person_b200.eval")
+    _, rc, ru = ref_shim.load()
+    stubs = {}
+    def stub(nm, **attrs):
+        m = types.ModuleType(nm); m.__dict__.update(attrs); stubs[nm] = m; sys.modules[nm] = m; return m
+    stub("matplotlib"); stub("matplotlib.pyplot"); stub("mpl_toolkits"); stub("mpl_toolkits.mplot3d", Axes3D=object)
+    pc = stub("pycalib"); pc.calib = stub("pycalib.calib", absolute_orientation=my_eval.absolute_orientation,
+                                          triangulate=ru.triangulate)
+    pc.plot = stub("pycalib.plot", plotCamera=lambda *a, **k: None)
+    sys.modules["util"] = ru
+    sys.path.insert(0, ref_shim.REF)
+    argv, sys.argv = sys.argv, ["x"]
+    try:
+        spec = _iu.spec_from_file_location("ref_eval", os.path.join(ref_shim.REF, "eval.py"))
+        re_ = _iu.module_from_spec(spec)
+        spec.loader.exec_module(re_)
+    finally:
+        sys.argv = argv
+        sys.path.remove(ref_shim.REF)
+        for k in list(stubs) + ["util", "argument"]:
+            sys.modules.pop(k, None)
+    kw = dict(C=4, N=24, seed=31, p_drop_2d=0.1, p_drop_3d=0.05)
+    sc = scene_mod.make_scene(**kw)
+    frame_skip, scale, width, height = 2, 0.01, 640, 360
+    gp2d, gs2d = np.array(sc.p2d), np.array(sc.s2d)
+    gp3d_w = np.array(sc.X_w)
+    gt = sc.t_gt.reshape(-1, 3, 1)
+    R, t = sc.R_init, sc.t_init.reshape(-1, 3, 1)
+    with quiet():
+        x_all = ru.triangulate_with_conf(gp2d, gs2d, sc.K, R, t, (gs2d > 0))
+        N, J = x_all.shape[:2]
+        nR, nt, _, _, np3d_w = re_.align(sc.R_gt, gt, R, t, x_all.reshape(-1, 3))
+        np3d_w = np3d_w.reshape(N, J, 3)
+        mask_3dw = np.all(~np.isnan(gp3d_w), axis=2)
+        E_x = np.linalg.norm(np3d_w[mask_3dw] - gp3d_w[mask_3dw], axis=1) * scale
+        E_R = np.array([ru.eval_R(sc.R_gt[i], nR[i]) for i in range(len(R))])
+        E_t = np.array([ru.eval_t(gt[i], nt[i]) for i in range(len(R))]) * scale
+        E_p, _, _, _ = re_.calc_repro_error(gs2d > 0, frame_skip, x_all, gp2d, sc.K, height, width, R, t)
+        with tempfile.TemporaryDirectory() as tmp:
+            jo = os.path.join(tmp, "e.json")
+            re_.eval_main(sc.K, R, t, sc.R_gt, gt, gp2d, gs2d, gp3d_w, frame_skip, width, height, jo, scale)
+            summary = open(jo).read()
+    np.savez_compressed(os.path.join(OUT, f"{name}.npz"), scene_kw=str(kw), frame_skip=frame_skip, scale=scale,
+                        E_R=E_R, E_t=E_t, E_p=E_p, E_x=E_x, nR=nR, nt=nt, summary=summary, versions=str(versions()))
+    print("wrote", name)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if len(sys.argv) > 1 and sys.argv[1] == "eval":
+        gen_eval()
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "linear":
         gen_linear()
         return
@@ -223,6 +281,7 @@ def main():
     gen_ransac("c3", dict(C=3, N=30, seed=22, sigma_px=1.0), 8, 7, 50.0, 5.0)
     gen_cli()
     gen_linear()
+    gen_eval()
 
 
 if __name__ == "__main__":

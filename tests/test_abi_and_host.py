@@ -83,6 +83,40 @@ def test_shard_ranges_cover_all_hypotheses():
             assert all(r[k][1] == r[k + 1][0] for k in range(world - 1))
 
 
+def test_chunk_plan_covers_every_hypothesis_once_with_equal_shares():
+    from calib_b200 import calib_ransac as cr
+    for n_iter in (1, 7, 4097, 50000, 100000):
+        for world in (1, 2, 3, 8):
+            plan = cr.chunk_plan(n_iter, world)
+            assert plan[0][0] == 0 and plan[-1][1] == n_iter
+            assert all(plan[i][1] == plan[i + 1][0] for i in range(len(plan) - 1))
+            assert all(0 <= o < world and b > a for a, b, o in plan)
+            share = [sum(b - a for a, b, o in plan if o == r) for r in range(world)]
+            assert sum(share) == n_iter
+            if n_iter >= 50000:
+                assert max(share) - min(share) <= len(plan)          # equal up to the rounding of the chunk size
+
+
+def test_eval_alignment_recovers_a_similarity_transform():
+    """eval.align / absolute_orientation (eval.py:29-63; pycalib restated, parity unpinned): cameras and points moved
+    by a known similarity transform come back exactly; E_R / E_t are then zero."""
+    from calib_b200 import eval as ev
+    from calib_b200 import scene
+    sc = scene.make_scene(C=5, N=4, seed=3)
+    rng = np.random.default_rng(0)
+    A = scene.rodrigues(rng.normal(0, 1.0, 3)); s0 = 2.7; d = rng.normal(0, 1, 3)
+    # estimated frame: X_e = (A^T (X_g - d)) / s0  ->  R_e = R_g A, t_e = (t_g + R_g d) / s0
+    R_e = np.array([R @ A for R in sc.R_gt])
+    t_e = np.array([(t.reshape(3) + R @ d) / s0 for R, t in zip(sc.R_gt, sc.t_gt)]).reshape(-1, 3, 1)
+    X_g = rng.normal(0, 1, (30, 3)); X_e = (X_g - d) @ A / s0
+    Rn, tn, _, _, Xn = ev.align(sc.R_gt, sc.t_gt.reshape(-1, 3, 1), R_e, t_e, X_e)
+    assert np.max(np.abs(Rn - sc.R_gt)) < 1e-12 and np.max(np.abs(tn - sc.t_gt.reshape(-1, 3, 1))) < 1e-11
+    assert np.max(np.abs(Xn - X_g)) < 1e-11
+    assert max(ev.eval_R(a, b) for a, b in zip(sc.R_gt, Rn)) < 1e-7 and ev.eval_t(sc.t_gt[0], tn[0]) < 1e-11
+    R, t, s = ev.absolute_orientation(X_e.T, X_g.T)
+    assert abs(s - s0) < 1e-12 and np.max(np.abs(R - A)) < 1e-12 and np.max(np.abs(t - d)) < 1e-12
+
+
 # ---------------------------------------------------------------- device math through the host emulation
 @pytest.fixture(scope="module")
 def emu():

@@ -128,3 +128,30 @@ def test_calib_linear_dropin_vs_reference_golden(golden_dir, tmp_path):
     camid2, K2, R2, t2 = dataio.load_cameras(os.path.join(prefix, "results", "linear_3_0.json"))
     assert np.array_equal(camid2, g["CAMID"]) and np.max(np.abs(R2 - g["R_linear"])) < 1e-9
     assert np.max(np.abs(t2 - g["t_linear"])) < 1e-9
+
+
+@pytest.mark.gpu
+def test_eval_metrics_vs_reference_golden(golden_dir, tmp_path, capsys):
+    """eval.eval_main on the arrays the reference's own eval.align / calc_repro_error / util.eval_R / eval_t /
+    triangulate_with_conf were run on (oracle/gen_golden.py gen_eval; pycalib.absolute_orientation restated there
+    and here alike — that one function is unpinned): error vectors 1e-8 relative, identical JSON summary."""
+    g = np.load(os.path.join(golden_dir, "eval_c4.npz"))
+    sc = scene.make_scene(**ast.literal_eval(str(g["scene_kw"])))
+    from calib_b200 import eval as ev
+    jo = str(tmp_path / "e.json")
+    E_R, E_t, E_p, E_x = ev.eval_main(sc.K, sc.R_init, sc.t_init.reshape(-1, 3, 1), sc.R_gt, sc.t_gt.reshape(-1, 3, 1),
+                                      np.array(sc.p2d), np.array(sc.s2d), np.array(sc.X_w), int(g["frame_skip"]), 640, 360,
+                                      jo, float(g["scale"]))
+    for mine, ref in ((E_R, g["E_R"]), (E_t, g["E_t"]), (E_p, g["E_p"]), (E_x, g["E_x"])):
+        assert mine.shape == ref.shape
+        assert np.max(np.abs(mine - ref)) < 1e-8 * max(1.0, np.nanmax(np.abs(ref)))
+    assert json.load(open(jo)) == json.loads(str(g["summary"]))
+    out = capsys.readouterr().out
+    assert "       Min  Median  Mean  Max" in out and "E_R:" in out and "E_x:" in out
+    from calib_b200 import ba
+    prob = ba.BAProblem(sc.K, np.array(sc.p2d), np.array(sc.s2d), None, None, ba.OP_BONE, 0.0, 0.0)
+    x_all = prob.triangulate(sc.R_init, sc.t_init)
+    prob.close()
+    E_p2, x_gt_all, _, _ = ev.calc_repro_error(np.array(sc.s2d) > 0, int(g["frame_skip"]), x_all, np.array(sc.p2d), sc.K,
+                                               360, 640, sc.R_init, sc.t_init)
+    assert np.allclose(E_p2, g["E_p"], rtol=1e-8, atol=1e-10) and x_gt_all.shape == np.array(sc.p2d).shape

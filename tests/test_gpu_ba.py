@@ -301,14 +301,18 @@ def test_observation_rebind(golden_dir):
     assert torch.equal(prob.residual(g["theta0"]), r0)
 
 
-@pytest.mark.parametrize("variant", ["0", "1", "2", "3"])
-def test_rj_kernel_variants_agree(monkeypatch, variant):
-    """Every store strategy of the fused residual + Jacobian kernel (LSU-staged and the TMA bulk-store variants)
-    returns the same blocks as the default one, ragged visibility included."""
-    sc = scene.make_scene(C=5, N=37, seed=41, score_mode="uniform", p_drop_2d=0.35, p_drop_3d=0.1)
+@pytest.mark.parametrize("N", [37, 38, 15, 256])
+@pytest.mark.parametrize("variant", ["1", "2", "3", "4", "5", "6", "7", "8", None])
+def test_rj_kernel_variants_agree(monkeypatch, variant, N):
+    """Every strategy of the fused residual + Jacobian kernel (LSU-staged, the TMA bulk-store variants, the persistent
+    TMA-pipelined variants and the default choice) returns bit for bit the blocks of the plain LSU kernel, ragged
+    visibility included.  N = 37: P = 629 is odd, the pipeline's 16-byte alignment rule sends it to the bulk-store
+    kernel; N = 38: P = 646 = two full 256-tiles + a 134-observation tail; N = 15: a single partial tile; N = 256:
+    full tiles only (P = 4352 = 17 x 256)."""
+    sc = scene.make_scene(C=5, N=N, seed=41, score_mode="uniform", p_drop_2d=0.35, p_drop_3d=0.1)
     sp2d, ss2d, sp3d, ss3d = scene.ba_inputs(sc)
     outs = []
-    for v in (None, variant):
+    for v in ("0", variant):
         if v is None:
             monkeypatch.delenv("BAX_RJ_VARIANT", raising=False)
         else:
@@ -320,3 +324,35 @@ def test_rj_kernel_variants_agree(monkeypatch, variant):
         prob.close()
     for a, b in zip(*outs):
         assert np.array_equal(a, b)
+
+
+def test_rj_pipeline_all_invisible_tiles_and_nan_scores():
+    """Tiles without a single visible observation (a camera that sees nothing for 300 frames), NaN scores and a
+    camera with no observation at all go through the pipelined kernel and match the oracle's Jacobian blocks."""
+    sc = scene.make_scene(C=4, N=400, seed=43, score_mode="uniform", p_drop_2d=0.1, p_drop_3d=0.1)
+    sp2d, ss2d, sp3d, ss3d = scene.ba_inputs(sc)
+    ss2d = ss2d.copy()
+    ss2d[1, 50:350] = 0.0                     # > 19 consecutive all-invisible 256-tiles in camera 1
+    ss2d[2, ::7, 3] = np.nan                  # NaN score == invisible (ss2d > 0 is False)
+    ss2d[3] = 0.0                             # camera 3 sees nothing
+    C, N, J = ss2d.shape
+    prob = ba.BAProblem(sc.K, sp2d, ss2d, sp3d, ss3d, ba.OP_BONE, 1.0, 1.0)
+    x0 = np.nan_to_num(sc.X_w[:, :J].reshape(-1, 3))
+    th = ba.to_theta(sc.R_init, sc.t_init, x0)
+    r2, Jc, Jp, oc, op = [t.cpu().numpy() for t in prob.residual_jacobian(th)]
+    args = (sc.K, sp2d.reshape(C, N * J, 2), ss2d, sp3d, ss3d, bo.OP_BONE, C, N, J, 1.0, 1.0)
+    f = bo.objfun(th, *args)
+    n_vis = int((ss2d > 0).sum())
+    assert r2.shape[0] == n_vis and not np.any(oc == 3)
+    assert np.max(np.abs(r2.reshape(-1) - f[:2 * n_vis])) < 1e-9 * np.max(np.abs(f))
+    Jd = bo.jacobian(th, *args).tocsr()[:2 * n_vis]
+    rows = np.arange(n_vis)
+    for a in range(2):
+        for k in range(6):
+            col = (3 * oc + k) if k < 3 else (3 * C + 3 * oc + (k - 3))
+            ref = np.asarray(Jd[2 * rows + a, col]).reshape(-1)
+            assert np.max(np.abs(Jc[:, a, k] - ref)) < 1e-9 * max(1.0, np.max(np.abs(ref)))
+        for k in range(3):
+            ref = np.asarray(Jd[2 * rows + a, 6 * C + 3 * op + k]).reshape(-1)
+            assert np.max(np.abs(Jp[:, a, k] - ref)) < 1e-9 * max(1.0, np.max(np.abs(ref)))
+    prob.close()
