@@ -397,11 +397,74 @@ def run_gpu(args):
     if line is not None:
         line["ransac"] = rs
         line["gpu_launches"] = int(launches) + sum(v["launches"] for v in rs["kernel_ms_one_pass"].values()) * max(1, min(args.steps, 3))
+    # ---------------- sweep leg, BASELINE configs[4]: independent cfg1-shaped problems (a bounded sample per GPU)
+    bt = batch_leg(rank, world, group, n_per_gpu=args.batch)
+    if line is not None and bt is not None:
+        line["batch"] = bt
     if rank == 0:
         print(json.dumps(line))
     prob.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def batch_leg(rank, world, group, n_per_gpu=32, n_streams=8):
+    """BASELINE configs[4] on a bounded sample: n_per_gpu x world independent 4-camera x 1000-frame problems
+    (cfg1 shape, one seed each), every one a complete ba_main run (triangulated start, reference tolerances), host
+    arrays in and host results out — dealt round-robin over the ranks, n_streams worker streams per GPU.  The
+    single-stream pass on rank 0's share is the launch-bound baseline the streams are there to beat."""
+    if n_per_gpu <= 0:
+        return None
+    import torch
+    import torch.distributed as dist
+    from calib_b200 import ba, scene
+    n = n_per_gpu * world
+    probs = []
+    for k in range(n):
+        if k % world != rank:
+            probs.append(None)            # never touched on this rank
+            continue
+        sc = scene.cfg1(seed=7000 + k, N=1000)
+        probs.append((sc.camid, sc.K, sc.R_init, sc.t_init) + tuple(scene.ba_inputs(sc)))
+    mine = [probs[k] for k in ba.batch_plan(n, rank, world)]
+    ba.ba_batch(mine[:min(len(mine), n_streams)], 1.0, 1.0, n_streams=n_streams)         # warm-up (pool, streams)
+
+    def run(ps, ns, grp):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        out = ba.ba_batch(ps, 1.0, 1.0, n_streams=ns, group=grp, gather=False, return_info=True)
+        torch.cuda.synchronize()
+        return time.perf_counter() - t0, out
+    t_multi, out = run(probs, n_streams, group)
+    work = float(sum(int((np.asarray(p[5]) > 0).sum()) * r[3]["iterations"] for p, r in zip(mine, out)))
+    iters = float(sum(r[3]["iterations"] for r in out))
+    if world > 1:
+        v = torch.tensor([t_multi], dtype=torch.float64, device="cuda")
+        dist.all_reduce(v, op=dist.ReduceOp.MAX)
+        t_multi = float(v[0])
+        s = torch.tensor([work, iters], dtype=torch.float64, device="cuda")
+        dist.all_reduce(s)
+        work, iters = float(s[0]), float(s[1])
+    res = {"metric": "BA problems/s (complete ba_main runs, host arrays in / out)", "value": n / t_multi, "unit": "problems/s",
+           "problems": n, "problems_per_gpu": n_per_gpu, "streams_per_gpu": n_streams, "wall_s": t_multi,
+           "lm_iterations": iters, "observations_per_s_per_lm_iteration": work / t_multi,
+           "config": {"workload": "cfg5 sample: independent 4-camera x 1000-frame x 17-joint problems (BASELINE configs[4] = 4096 of them)",
+                      "sharding": f"problems dealt round-robin over {world} GPU(s); replicas only, no data-path collective"}}
+    if rank == 0:
+        t_single, _ = run_local_single(mine, ba)
+        res["single_stream_problems_per_s_one_gpu"] = len(mine) / t_single
+    return res
+
+
+def run_local_single(mine, ba):
+    import torch
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    out = ba.ba_batch(mine, 1.0, 1.0, n_streams=1)
+    torch.cuda.synchronize()
+    return time.perf_counter() - t0, out
 
 
 def main():
@@ -412,6 +475,7 @@ def main():
     ap.add_argument("--workload", default="cfg4shard", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--batch", type=int, default=32, help="problems per GPU of the sweep leg (0 = skip)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3

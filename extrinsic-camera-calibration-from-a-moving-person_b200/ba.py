@@ -587,3 +587,93 @@ def ba_main(camid, K, R_w2c, t_w2c, sp2d, ss2d, sp3d, ss3d, lambda1, lambda2, *,
         prob.close()
     R, t, x = from_theta(theta, C)
     return (R, t, x, res) if return_info else (R, t, x)
+
+
+# ----------------------------------------------------------------------------- batches of independent problems
+def batch_plan(n_problems, rank=0, world=1):
+    """Problem indices owned by `rank`: round-robin (problem k -> rank k % world), so that a sweep whose cost
+    drifts with the index (longer sequences last) still loads every GPU alike.  Replicas only — the problems
+    of BASELINE configs[4] (4096 independent 4-camera scenes) share nothing, so there is no collective on the
+    data path; only the results are gathered."""
+    return list(range(rank, n_problems, world))
+
+
+def ba_batch(problems, lambda1, lambda2, *, n_streams=8, group=None, gather=True, solve=None, **kw):
+    """Multi-sequence sweep: `ba_main` on every entry of `problems` — a sequence of
+    (camid, K, R_w2c, t_w2c, sp2d, ss2d, sp3d, ss3d) tuples (or callables returning one, so a sweep need not
+    hold every scene in host memory) — each by the same code path and therefore with the same result as a
+    single `ba_main` call.
+
+    One GPU: `n_streams` worker threads, each with its own CUDA stream and its own libbax handle, pull problem
+    indices from a shared queue.  A 4-camera problem is launch- and latency-bound on its own (a few hundred CTAs
+    per kernel, ~40 launches and 2-3 scalar read-backs per trust-region iteration); the streams overlap the
+    kernels of one problem with the read-backs and host logic of the others.  ctypes releases the GIL for the
+    duration of every libbax call, read-backs included.
+    Several GPUs: pass a torch.distributed `group`; problems are dealt round-robin over the ranks (batch_plan),
+    every rank solves its own, and with gather=True the results are all-gathered so that every rank returns
+    the full list (index order).  -> list of (R, t, x) (or (R, t, x, info) with return_info=True)."""
+    import queue
+    import threading
+    n = len(problems)
+    rank, world = 0, 1
+    if group is not None:
+        import torch.distributed as dist
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+    mine = batch_plan(n, rank, world)
+    if solve is None:
+        if not torch.cuda.is_available():
+            raise BaxError("no CUDA device: this package has no CPU fallback")
+        solve = ba_main
+        kw.setdefault("verbose", False)
+    results = {}
+    errors = []
+    q = queue.SimpleQueue()
+    for k in mine:
+        q.put(k)
+
+    def worker():
+        cuda = torch.cuda.is_available()
+        ctx = torch.cuda.stream(torch.cuda.Stream()) if cuda else None
+        if ctx is not None:
+            ctx.__enter__()
+        try:
+            while not errors:
+                try:
+                    k = q.get_nowait()
+                except queue.Empty:
+                    return
+                p = problems[k]() if callable(problems[k]) else problems[k]
+                results[k] = solve(*p, lambda1, lambda2, **kw)
+        except BaseException as e:          # surfaced by the caller, with the failing problem's index
+            errors.append((k, e))
+        finally:
+            if ctx is not None:
+                ctx.__exit__(None, None, None)
+
+    n_thr = max(1, min(int(n_streams), len(mine)))
+    if n_thr == 1:
+        worker()
+    else:
+        dev = torch.cuda.current_device() if torch.cuda.is_available() else None
+
+        def entry():
+            if dev is not None:
+                torch.cuda.set_device(dev)
+            worker()
+        threads = [threading.Thread(target=entry, name=f"ba_batch-{i}") for i in range(n_thr)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+    if errors:
+        k, e = errors[0]
+        raise type(e)(f"ba_batch: problem {k}: {e}") from e
+    if group is not None and gather:
+        import torch.distributed as dist
+        parts = [None] * world
+        dist.all_gather_object(parts, results, group=group)
+        results = {}
+        for part in parts:
+            results.update(part)
+        return [results[k] for k in range(n)]
+    return [results[k] for k in mine]

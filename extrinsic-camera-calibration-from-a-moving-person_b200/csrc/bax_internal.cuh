@@ -21,6 +21,10 @@ void bax_set_error(const char* fmt, ...);
     }                                                                                      \
   } while (0)
 #define BAX_LAUNCH_CHECK() BAX_CUDA(cudaGetLastError())
+struct bax_handle;
+cudaError_t bax_dev_alloc(bax_handle* h, void** p, size_t bytes);   // stream-ordered (bax_problem.cu)
+void bax_dev_free(bax_handle* h, void* p);
+#define BAX_ALLOC(h, ptr, bytes) BAX_CUDA(bax_dev_alloc((h), (void**)&(ptr), (bytes)))
 
 struct bax_handle {
   int device;
@@ -74,6 +78,7 @@ struct bax_handle {
   double* partials;          // generic per-block partial sums
   size_t partials_bytes;
   double* host_pinned;       // small pinned staging for scalars
+  cudaStream_t mem_stream;   // stream of the last bax_problem_set: the handle's device memory is allocated and freed in its order
   // ---- timing
   int dense_coop;            // 1: cooperative multi-CTA reduced solve (env BAX_DENSE_COOP=0 selects the single-CTA kernel)
   int rj_variant;            // tuning knob (env BAX_RJ_VARIANT): -1 = auto [default: 5 or 4]; 0 = per-warp staged LSU stores; 1/2/3 = CTA-staged TMA bulk stores (256x4, 128x8, 256x3); 4..8 = persistent TMA pipeline (stages x CTAs/SM: 2x3, 4x2, 3x2, 5x2, 8x1)

@@ -308,12 +308,14 @@ __global__ void k_reduce_max(const double* __restrict__ v, int n, double* __rest
 
 static int ensure_trial_buffers(bax_handle* h) {
   if (!h->Yhat) {
-    BAX_CUDA(cudaMalloc(&h->Yhat, sizeof(double) * (size_t)h->R * h->ldy));
-    BAX_CUDA(cudaMemset(h->Yhat, 0, sizeof(double) * (size_t)h->R * h->ldy));
+    BAX_ALLOC(h, h->Yhat, sizeof(double) * (size_t)h->R * h->ldy);
+    BAX_CUDA(cudaMemsetAsync(h->Yhat, 0, sizeof(double) * (size_t)h->R * h->ldy, h->mem_stream));
+    BAX_CUDA(cudaStreamSynchronize(h->mem_stream));
   }
   if (!h->Gv && h->Nv > 0) {
-    BAX_CUDA(cudaMalloc(&h->Gv, sizeof(double) * (size_t)(3 * h->C + 1) * h->ldv));
-    BAX_CUDA(cudaMemset(h->Gv, 0, sizeof(double) * (size_t)(3 * h->C + 1) * h->ldv));
+    BAX_ALLOC(h, h->Gv, sizeof(double) * (size_t)(3 * h->C + 1) * h->ldv);
+    BAX_CUDA(cudaMemsetAsync(h->Gv, 0, sizeof(double) * (size_t)(3 * h->C + 1) * h->ldv, h->mem_stream));
+    BAX_CUDA(cudaStreamSynchronize(h->mem_stream));
   }
   return BAX_OK;
 }

@@ -148,16 +148,29 @@ extern "C" int bax_create(int device, bax_handle** out) {
   BAX_CUDA(cudaEventCreate(&h->ev0));
   BAX_CUDA(cudaEventCreate(&h->ev1));
   BAX_CUDA(cudaMallocHost((void**)&h->host_pinned, 64 * sizeof(double)));
+  {  // freed blocks stay in the device's default pool: the next handle of a sweep gets them back without a driver call
+    cudaMemPool_t pool; unsigned long long keep = ~0ULL;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+  }
   *out = h;
   return BAX_OK;
+}
+
+// Device memory of a handle is stream-ordered (cudaMallocAsync / cudaFreeAsync on the stream of the last
+// bax_problem_set): creating and destroying a handle per problem of a multi-sequence sweep costs no cudaMalloc /
+// cudaFree, and — unlike cudaFree — releasing one problem does not synchronise the streams of the others.
+cudaError_t bax_dev_alloc(bax_handle* h, void** p, size_t bytes) { return cudaMallocAsync(p, bytes ? bytes : 8, h->mem_stream); }
+void bax_dev_free(bax_handle* h, void* p) {
+  if (!p) return;
+  if (cudaFreeAsync(p, h->mem_stream) != cudaSuccess) { cudaGetLastError(); cudaFree(p); }   // the stream no longer exists
 }
 
 static void free_problem(bax_handle* h) {
   void* ptrs[] = {(void*)h->K, h->bones, h->joint_bones, h->dhat, h->blockbase, h->campack, h->campack_lin, h->Vp, h->gp,
                   h->Hcc, h->gc, h->Lbar, h->rb, h->Yhat, h->Gv, h->syrk_part, h->dense_ws, h->coef,
                   h->partials, h->saved.Vp, h->saved.gp, h->saved.lin, h->saved.Lbar, h->saved.rb, h->saved.campack_lin};
-  for (void* p : ptrs) if (p) cudaFree(p);
-  for (int i = 0; i < 8; ++i) { if (h->buf[i]) cudaFree(h->buf[i]); h->buf[i] = nullptr; }
+  for (void* p : ptrs) bax_dev_free(h, p);
+  for (int i = 0; i < 8; ++i) { bax_dev_free(h, h->buf[i]); h->buf[i] = nullptr; }
   h->K = nullptr; h->bones = nullptr; h->joint_bones = nullptr; h->dhat = nullptr; h->blockbase = nullptr;
   h->campack = nullptr; h->campack_lin = nullptr; h->Vp = h->gp = h->Hcc = h->gc = h->Lbar = h->rb = nullptr;
   h->Yhat = h->Gv = h->syrk_part = h->dense_ws = h->coef = h->partials = nullptr;
@@ -184,6 +197,7 @@ extern "C" int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B
   cudaStream_t s = (cudaStream_t)stream;
   BAX_CUDA(cudaSetDevice(h->device));
   free_problem(h);
+  h->mem_stream = s;
   h->C = C; h->N = N; h->J = J; h->J3 = J3; h->B = B; h->P = (int64_t)N * J;
   h->lam1 = lambda1; h->lam2 = lambda2; h->n_frames_global = N;
   h->y2d = y2d; h->s2d = s2d;
@@ -196,10 +210,10 @@ extern "C" int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B
     }
     h->bones_host[2 * b] = a0; h->bones_host[2 * b + 1] = a1;
   }
-  double* Kd; BAX_CUDA(cudaMalloc(&Kd, sizeof(double) * 9 * C));
+  double* Kd; BAX_ALLOC(h, Kd, sizeof(double) * 9 * C);
   BAX_CUDA(cudaMemcpyAsync(Kd, K, sizeof(double) * 9 * C, cudaMemcpyDeviceToDevice, s));
   h->K = Kd;
-  BAX_CUDA(cudaMalloc(&h->bones, sizeof(int32_t) * 2 * (B > 0 ? B : 1)));
+  BAX_ALLOC(h, h->bones, sizeof(int32_t) * 2 * (B > 0 ? B : 1));
   BAX_CUDA(cudaMemcpyAsync(h->bones, h->bones_host, sizeof(int32_t) * 2 * B, cudaMemcpyHostToDevice, s));
   {  // joint -> incident bones
     size_t n = (size_t)J * BAX_MAX_JB * 2;
@@ -213,7 +227,7 @@ extern "C" int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B
         jb[((size_t)j * BAX_MAX_JB + k) * 2] = b;
         jb[((size_t)j * BAX_MAX_JB + k) * 2 + 1] = e == 0 ? 1 : -1;
       }
-    BAX_CUDA(cudaMalloc(&h->joint_bones, n * sizeof(int32_t)));
+    BAX_ALLOC(h, h->joint_bones, n * sizeof(int32_t));
     BAX_CUDA(cudaMemcpyAsync(h->joint_bones, jb, n * sizeof(int32_t), cudaMemcpyHostToDevice, s));
     BAX_CUDA(cudaStreamSynchronize(s));
     free(jb);
@@ -223,14 +237,14 @@ extern "C" int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B
   if (p3d && s3d && B > 0) {
     int64_t NB = (int64_t)N * B;
     int32_t* flag; int64_t *f64, *pos;
-    BAX_CUDA(cudaMalloc(&flag, NB * sizeof(int32_t)));
-    BAX_CUDA(cudaMalloc(&f64, NB * sizeof(int64_t)));
-    BAX_CUDA(cudaMalloc(&pos, NB * sizeof(int64_t)));
+    BAX_ALLOC(h, flag, NB * sizeof(int32_t));
+    BAX_ALLOC(h, f64, NB * sizeof(int64_t));
+    BAX_ALLOC(h, pos, NB * sizeof(int64_t));
     int nb = (int)((NB + 255) / 256);
     k_bone_dir_flags<<<nb, 256, 0, s>>>(p3d, s3d, h->bones, C, N, J3, B, flag);
     k_flag_to_i64<<<nb, 256, 0, s>>>(flag, NB, f64);
     size_t tb = 0; cub::DeviceScan::ExclusiveSum(nullptr, tb, f64, pos, NB, s);
-    void* tmp; BAX_CUDA(cudaMalloc(&tmp, tb ? tb : 8));
+    void* tmp; BAX_ALLOC(h, tmp, tb ? tb : 8);
     cub::DeviceScan::ExclusiveSum(tmp, tb, f64, pos, NB, s);
     int64_t lastp = 0; int32_t lastf = 0;
     BAX_CUDA(cudaMemcpyAsync(&lastp, pos + NB - 1, 8, cudaMemcpyDeviceToHost, s));
@@ -238,44 +252,44 @@ extern "C" int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B
     BAX_CUDA(cudaStreamSynchronize(s));
     h->Nv = lastp + lastf;
     if (h->Nv > 0) {
-      BAX_CUDA(cudaMalloc(&h->dhat, sizeof(double) * 3 * C * h->Nv));
+      BAX_ALLOC(h, h->dhat, sizeof(double) * 3 * C * h->Nv);
       k_bone_dir_scatter<<<nb, 256, 0, s>>>(p3d, h->bones, flag, pos, C, N, J3, B, h->Nv, h->dhat);
       BAX_LAUNCH_CHECK();
     }
     BAX_CUDA(cudaStreamSynchronize(s));
-    cudaFree(flag); cudaFree(f64); cudaFree(pos); cudaFree(tmp);
+    bax_dev_free(h, flag); bax_dev_free(h, f64); bax_dev_free(h, pos); bax_dev_free(h, tmp);
   }
   // ---- residual row order: exclusive scan of visible counts over (camera, 256-point block)
   h->nblk_obs = (int)((h->P + 255) / 256);
   {
     int64_t nb = (int64_t)C * h->nblk_obs;
-    int64_t* cnt; BAX_CUDA(cudaMalloc(&cnt, nb * sizeof(int64_t)));
-    BAX_CUDA(cudaMalloc(&h->blockbase, nb * sizeof(int64_t)));
+    int64_t* cnt; BAX_ALLOC(h, cnt, nb * sizeof(int64_t));
+    BAX_ALLOC(h, h->blockbase, nb * sizeof(int64_t));
     k_count_visible<<<dim3(h->nblk_obs, C), 256, 0, s>>>(s2d, h->P, cnt);
     size_t tb = 0; cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, h->blockbase, nb, s);
-    void* tmp; BAX_CUDA(cudaMalloc(&tmp, tb ? tb : 8));
+    void* tmp; BAX_ALLOC(h, tmp, tb ? tb : 8);
     cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, h->blockbase, nb, s);
     int64_t lb = 0, lc = 0;
     BAX_CUDA(cudaMemcpyAsync(&lb, h->blockbase + nb - 1, 8, cudaMemcpyDeviceToHost, s));
     BAX_CUDA(cudaMemcpyAsync(&lc, cnt + nb - 1, 8, cudaMemcpyDeviceToHost, s));
     BAX_CUDA(cudaStreamSynchronize(s));
     h->n_vis = lb + lc;
-    cudaFree(cnt); cudaFree(tmp);
+    bax_dev_free(h, cnt); bax_dev_free(h, tmp);
   }
   // ---- state buffers
   const int C6 = 6 * C;
-  BAX_CUDA(cudaMalloc(&h->campack, sizeof(double) * CAMPACK * C));
-  BAX_CUDA(cudaMalloc(&h->campack_lin, sizeof(double) * CAMPACK * C));
-  BAX_CUDA(cudaMalloc(&h->Vp, sizeof(double) * 6 * h->P));
-  BAX_CUDA(cudaMalloc(&h->gp, sizeof(double) * 3 * h->P));
-  BAX_CUDA(cudaMalloc(&h->Lbar, sizeof(double) * BAX_MAX_B));
-  BAX_CUDA(cudaMalloc(&h->rb, sizeof(double) * BAX_MAX_B));
+  BAX_ALLOC(h, h->campack, sizeof(double) * CAMPACK * C);
+  BAX_ALLOC(h, h->campack_lin, sizeof(double) * CAMPACK * C);
+  BAX_ALLOC(h, h->Vp, sizeof(double) * 6 * h->P);
+  BAX_ALLOC(h, h->gp, sizeof(double) * 3 * h->P);
+  BAX_ALLOC(h, h->Lbar, sizeof(double) * BAX_MAX_B);
+  BAX_ALLOC(h, h->rb, sizeof(double) * BAX_MAX_B);
   BAX_CUDA(cudaMemsetAsync(h->Lbar, 0, sizeof(double) * BAX_MAX_B, s));
   BAX_CUDA(cudaMemsetAsync(h->rb, 0, sizeof(double) * BAX_MAX_B, s));
-  BAX_CUDA(cudaMalloc(&h->coef, sizeof(double) * (C6 + BAX_MAX_B)));
-  BAX_CUDA(cudaMalloc(&h->dense_ws, sizeof(double) * ((size_t)C6 * C6 + (size_t)BAX_MAX_B * C6 * 2 + 4 * C6 + 1024)));
+  BAX_ALLOC(h, h->coef, sizeof(double) * (C6 + BAX_MAX_B));
+  BAX_ALLOC(h, h->dense_ws, sizeof(double) * ((size_t)C6 * C6 + (size_t)BAX_MAX_B * C6 * 2 + 4 * C6 + 1024));
   h->partials_bytes = sizeof(double) * (size_t)(1 << 22);
-  BAX_CUDA(cudaMalloc(&h->partials, h->partials_bytes));
+  BAX_ALLOC(h, h->partials, h->partials_bytes);
   h->buf_count[BAX_BUF_BONE] = B + 1;
   h->buf_count[BAX_BUF_COST] = B + 2;
   h->buf_count[BAX_BUF_LIN] = (int64_t)C6 * C6 + C6 + B + 2;
@@ -285,7 +299,7 @@ extern "C" int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B
   h->buf_count[BAX_BUF_NORM] = 4;
   h->buf_count[BAX_BUF_GMAX] = 2;
   for (int i = 0; i < 8; ++i) {
-    BAX_CUDA(cudaMalloc(&h->buf[i], sizeof(double) * (h->buf_count[i] > 0 ? h->buf_count[i] : 1)));
+    BAX_ALLOC(h, h->buf[i], sizeof(double) * (h->buf_count[i] > 0 ? h->buf_count[i] : 1));
     BAX_CUDA(cudaMemsetAsync(h->buf[i], 0, sizeof(double) * (h->buf_count[i] > 0 ? h->buf_count[i] : 1), s));
   }
   // Yhat / Gv are allocated lazily by the first linearise (bax_lm.cu)
@@ -308,12 +322,13 @@ extern "C" int bax_linearize_push(bax_handle* h) {
   if (!h || !h->campack) { bax_set_error("bax_linearize_push: no problem"); return BAX_E_ARG; }
   BAX_CUDA(cudaSetDevice(h->device));
   if (!h->saved.Vp) {
-    BAX_CUDA(cudaMalloc(&h->saved.Vp, sizeof(double) * 6 * h->P));
-    BAX_CUDA(cudaMalloc(&h->saved.gp, sizeof(double) * 3 * h->P));
-    BAX_CUDA(cudaMalloc(&h->saved.lin, sizeof(double) * h->buf_count[BAX_BUF_LIN]));
-    BAX_CUDA(cudaMalloc(&h->saved.Lbar, sizeof(double) * BAX_MAX_B));
-    BAX_CUDA(cudaMalloc(&h->saved.rb, sizeof(double) * BAX_MAX_B));
-    BAX_CUDA(cudaMalloc(&h->saved.campack_lin, sizeof(double) * CAMPACK * h->C));
+    BAX_ALLOC(h, h->saved.Vp, sizeof(double) * 6 * h->P);
+    BAX_ALLOC(h, h->saved.gp, sizeof(double) * 3 * h->P);
+    BAX_ALLOC(h, h->saved.lin, sizeof(double) * h->buf_count[BAX_BUF_LIN]);
+    BAX_ALLOC(h, h->saved.Lbar, sizeof(double) * BAX_MAX_B);
+    BAX_ALLOC(h, h->saved.rb, sizeof(double) * BAX_MAX_B);
+    BAX_ALLOC(h, h->saved.campack_lin, sizeof(double) * CAMPACK * h->C);
+    BAX_CUDA(cudaStreamSynchronize(h->mem_stream));
   }
   swap_lin_state(h);
   h->saved.valid = 1;

@@ -280,9 +280,10 @@ __global__ void k_syrk96_reduce(const double* __restrict__ part, int rows, int n
 
 static int ensure_part(bax_handle* h, size_t need) {
   if (need > h->syrk_part_bytes) {
-    if (h->syrk_part) cudaFree(h->syrk_part);
+    bax_dev_free(h, h->syrk_part);
     h->syrk_part = nullptr; h->syrk_part_bytes = 0;
-    BAX_CUDA(cudaMalloc(&h->syrk_part, need));
+    BAX_ALLOC(h, h->syrk_part, need);
+    BAX_CUDA(cudaStreamSynchronize(h->mem_stream));
     h->syrk_part_bytes = need;
   }
   return BAX_OK;

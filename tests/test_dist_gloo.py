@@ -100,3 +100,44 @@ def _ba_sum_case(rank, world):
 def test_ba_packed_sums_two_ranks():
     for e_blocks, e_var in _run(_ba_sum_case):
         assert e_blocks < 1e-12 and e_var < 1e-14
+
+
+def _fake_solve(camid, K, R, t, sp2d, ss2d, sp3d, ss3d, lambda1, lambda2, **kw):
+    """Stand-in for ba_main in the CPU tests of the sweep plumbing: a deterministic function of the problem."""
+    return (R * lambda1, t + lambda2, np.full((2, 3), float(camid[0])))
+
+
+def _batch_case(rank, world):
+    from calib_b200 import ba
+    n = 11
+    probs = [(np.array([k]), None, np.full((2, 3, 3), float(k)), np.full((2, 3, 1), 0.5 * k), None, None, None, None)
+             for k in range(n)]
+    lazy = [(lambda p=p: p) for p in probs]                    # problems may be given as callables
+    full = ba.ba_batch(lazy, 2.0, 3.0, n_streams=3, group=dist.group.WORLD, solve=_fake_solve)
+    local = ba.ba_batch(probs, 2.0, 3.0, n_streams=1, group=dist.group.WORLD, gather=False, solve=_fake_solve)
+    return ([float(r[2][0, 0]) for r in full], [float(r[0][0, 0, 0]) for r in full], [float(r[2][0, 0]) for r in local])
+
+
+def test_ba_batch_sweep_two_ranks():
+    """BASELINE configs[4] plumbing: problems dealt round-robin over the ranks, solved by worker threads, results
+    gathered in index order on every rank (replicas only — no data-path collective)."""
+    r0, r1 = _run(_batch_case)
+    assert r0[0] == r1[0] == [float(k) for k in range(11)]
+    assert r0[1] == [2.0 * k for k in range(11)]
+    assert r0[2] == [float(k) for k in range(0, 11, 2)] and r1[2] == [float(k) for k in range(1, 11, 2)]
+
+
+def test_ba_batch_plan_and_errors():
+    from calib_b200 import ba
+    for n in (0, 1, 5, 4096):
+        for world in (1, 2, 8):
+            plans = [ba.batch_plan(n, r, world) for r in range(world)]
+            assert sorted(k for p in plans for k in p) == list(range(n))
+            assert max(len(p) for p in plans) - min(len(p) for p in plans) <= 1
+
+    def boom(*a, **k):
+        raise ValueError("Initial guess is outside of provided bounds")
+    with pytest.raises(ValueError, match="problem 0"):
+        ba.ba_batch([(np.array([0]),) + (None,) * 7], 1.0, 1.0, solve=boom)
+    with pytest.raises(calib_b200._lib.BaxError if not torch.cuda.is_available() else Exception):
+        ba.ba_batch([(np.array([0]),) + (None,) * 7], 1.0, 1.0)     # no solve given: the CUDA path, no CPU fallback

@@ -356,3 +356,24 @@ def test_rj_pipeline_all_invisible_tiles_and_nan_scores():
             ref = np.asarray(Jd[2 * rows + a, 6 * C + 3 * op + k]).reshape(-1)
             assert np.max(np.abs(Jp[:, a, k] - ref)) < 1e-9 * max(1.0, np.max(np.abs(ref)))
     prob.close()
+
+
+def test_ba_batch_equals_single_problem_runs():
+    """BASELINE configs[4] (batch of independent 4-camera problems): the multi-stream sweep returns, problem by
+    problem, bit for bit what a single ba_main call returns (same kernels, same order of operations), whatever
+    the number of worker streams; a failing problem is reported with its index."""
+    probs = []
+    for k in range(7):
+        sc = scene.make_scene(C=4, N=20 + 3 * k, seed=100 + k, score_mode="uniform", p_drop_2d=0.15, p_drop_3d=0.1)
+        sp2d, ss2d, sp3d, ss3d = scene.ba_inputs(sc)
+        probs.append((sc.camid, sc.K, sc.R_init, sc.t_init, sp2d, ss2d, sp3d, ss3d))
+    single = [ba.ba_main(*p, 1.0, 10.0, verbose=False) for p in probs]
+    for n_streams in (1, 4):
+        batch = ba.ba_batch(probs, 1.0, 10.0, n_streams=n_streams)
+        assert len(batch) == len(single)
+        for (R0, t0, x0), (R1, t1, x1) in zip(single, batch):
+            assert np.array_equal(R0, R1) and np.array_equal(t0, t1) and np.array_equal(x0, x1)
+    bad = list(probs[2])
+    bad[5] = np.zeros_like(bad[5])                  # nothing visible: NaN start, as in the reference
+    with pytest.raises(ValueError, match="problem 1"):
+        ba.ba_batch([probs[0], tuple(bad), probs[1]], 1.0, 10.0, n_streams=2)
