@@ -360,6 +360,20 @@ def run_gpu(args):
     torch.cuda.synchronize()
     shares = {k: {"ms": round(v[0], 4), "launches": v[1]} for k, v in prob.timing_read().items() if v[1]}
     prob.timing(False)
+    comm = None
+    if world > 1:      # device time inside the all-reduces (waiting for the slowest rank included), separate pass
+        names = ["bone", "cost", "lin", "schur", "rhs2", "step", "norm", "gmax"]
+        sol = ba.TRFSolver(prob, theta0, ftol=0.0, xtol=0.0, gtol=0.0)
+        prob.comm_events = []
+        barrier()
+        ev0.record()
+        for _ in range(6):
+            sol.iterate()
+        ev1.record()
+        torch.cuda.synchronize()
+        comm = {names[k]: {"calls": v[0], "ms": round(v[1], 4), "doubles": v[2]} for k, v in prob.comm_timing_read().items()}
+        comm["ms_6_steps"] = ev0.elapsed_time(ev1)
+        prob.comm_events = None
 
     line = None
     if rank == 0:
@@ -389,7 +403,7 @@ def run_gpu(args):
                         "note": "every step: pinned-host observations + theta -> device, one full LM iteration "
                                 "(linearise, solves, cost evaluations), theta -> host; same solve-restart rule as value; the upload of step "
                                 "k+1 (second device buffer, copy stream) overlaps the kernels of step k"},
-                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "comm": comm,
                 "clocks": sampler.summary()}
     # ---------------- RANSAC leg (hypotheses/s), BASELINE configs[1]
     from calib_b200 import calib_ransac as cr
@@ -408,7 +422,7 @@ def run_gpu(args):
         dist.destroy_process_group()
 
 
-def batch_leg(rank, world, group, n_per_gpu=32, n_streams=8):
+def batch_leg(rank, world, group, n_per_gpu=64, n_streams=16):
     """BASELINE configs[4] on a bounded sample: n_per_gpu x world independent 4-camera x 1000-frame problems
     (cfg1 shape, one seed each), every one a complete ba_main run (triangulated start, reference tolerances), host
     arrays in and host results out — dealt round-robin over the ranks, n_streams worker streams per GPU.  The
@@ -475,7 +489,7 @@ def main():
     ap.add_argument("--workload", default="cfg4shard", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--batch", type=int, default=32, help="problems per GPU of the sweep leg (0 = skip)")
+    ap.add_argument("--batch", type=int, default=64, help="problems per GPU of the sweep leg (0 = skip)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3

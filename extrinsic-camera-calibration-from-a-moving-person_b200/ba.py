@@ -127,6 +127,7 @@ class BAProblem:
             self.n_vis, self.n_v3d, self.m, self.n, self.aug_rows, _ = [int(v) for v in d]
             self.step = torch.zeros(self.n, **f)
         self.group = group
+        self.comm_events = None
         self._views = {}
         if n_frames_global is not None:
             check(self.L.bax_set_global_frames(self.h, int(n_frames_global)), "bax_set_global_frames")
@@ -167,8 +168,23 @@ class BAProblem:
         key = (which, p.value)                 # the LIN buffer changes address on linearize_push / _pop
         if key not in self._views:
             self._views[key] = torch.as_tensor(_DevView(p.value, n.value), device=self.dev)
-        which = key
-        dist.all_reduce(self._views[which], op=op or dist.ReduceOp.SUM, group=self.group)
+        if self.comm_events is not None:            # bench instrumentation: device time spent in (and waiting for) the collective
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            dist.all_reduce(self._views[key], op=op or dist.ReduceOp.SUM, group=self.group)
+            e1.record()
+            self.comm_events.append((which, n.value, e0, e1))
+            return
+        dist.all_reduce(self._views[key], op=op or dist.ReduceOp.SUM, group=self.group)
+
+    def comm_timing_read(self):
+        """{buffer: (calls, total ms, doubles per call)} of the all-reduces recorded since comm_events was set to []."""
+        torch.cuda.synchronize(self.dev)
+        out = {}
+        for which, cnt, e0, e1 in self.comm_events or []:
+            c, ms, _ = out.get(which, (0, 0.0, cnt))
+            out[which] = (c + 1, ms + e0.elapsed_time(e1), cnt)
+        return out
 
     # ---- reference-shaped evaluations
     def residual(self, theta):
@@ -598,7 +614,7 @@ def batch_plan(n_problems, rank=0, world=1):
     return list(range(rank, n_problems, world))
 
 
-def ba_batch(problems, lambda1, lambda2, *, n_streams=8, group=None, gather=True, solve=None, **kw):
+def ba_batch(problems, lambda1, lambda2, *, n_streams=16, group=None, gather=True, solve=None, **kw):
     """Multi-sequence sweep: `ba_main` on every entry of `problems` — a sequence of
     (camid, K, R_w2c, t_w2c, sp2d, ss2d, sp3d, ss3d) tuples (or callables returning one, so a sweep need not
     hold every scene in host memory) — each by the same code path and therefore with the same result as a

@@ -377,3 +377,41 @@ def test_ba_batch_equals_single_problem_runs():
     bad[5] = np.zeros_like(bad[5])                  # nothing visible: NaN start, as in the reference
     with pytest.raises(ValueError, match="problem 1"):
         ba.ba_batch([probs[0], tuple(bad), probs[1]], 1.0, 10.0, n_streams=2)
+
+
+@pytest.mark.parametrize("which", ["cfg3", "cfg4shard"])
+def test_full_size_configs_vs_oracle_and_step_identity(which):
+    """BASELINE configs[2] at full size (31 cameras x 10 000 frames x 17 joints, 30 % dropped detections: 3.7e6
+    observations, 510 186 parameters) and one GPU's shard of configs[3] (64 cameras x 12 500 frames: 1.36e7
+    observations).  One oracle evaluation of ba.objfun is affordable at these sizes (seconds): residual vector
+    1e-9.  The damped Schur step is checked through an identity that needs no assembled Jacobian: with
+    (J^T J + alpha I) p = -g,  |J p|^2 = -g.p - alpha |p|^2,  J p taken as a central difference of the GPU
+    residual along p."""
+    sc = scene.cfg3(seed=5) if which == "cfg3" else scene.cfg4(seed=5, N=12500, C=64)
+    sp2d, ss2d, sp3d, ss3d = scene.ba_inputs(sc)
+    C, N, J = ss2d.shape
+    lam1, lam2 = (100.0, 1.0) if which == "cfg3" else (1.0, 1.0)
+    prob = ba.BAProblem(sc.K, sp2d, ss2d, sp3d, ss3d, ba.OP_BONE, lam1, lam2)
+    x0 = prob.triangulate(sc.R_init, sc.t_init)
+    th = ba.to_theta(sc.R_init, sc.t_init, x0.reshape(-1, 3))
+    assert np.all(np.isfinite(th))
+    r = prob.residual(th)
+    f = bo.objfun(th, sc.K, sp2d.reshape(C, N * J, 2), ss2d, sp3d, ss3d, bo.OP_BONE, C, N, J, lam1, lam2)
+    assert r.shape[0] == f.shape[0] == 2 * prob.n_vis + prob.n_v3d + 12
+    assert _rel(r.cpu().numpy(), f) <= 1e-9
+    cost, ginf, g2, xn = prob.linearize(th)
+    assert abs(cost - 0.5 * float(f @ f)) <= 1e-11 * cost
+    alpha = 1e-3 * g2 / xn
+    pn2, gp, ptq = prob.trial(alpha, True)
+    assert gp < 0 and pn2 > 0 and ptq > 0
+    p = prob.step.clone()
+    thd = prob._dev_theta(th)
+    eps = 1e-4 / float(p.abs().max())
+    Jp = (prob.residual(thd + eps * p).clone() - prob.residual(thd - eps * p)) / (2 * eps)
+    lhs = float(Jp @ Jp)
+    rhs = -gp - alpha * pn2
+    assert abs(lhs - rhs) <= 1e-6 * rhs
+    # first-order decrease: g.p is the directional derivative of the cost along p
+    dcost = (prob.cost(thd + eps * p) - prob.cost(thd - eps * p)) / (2 * eps)
+    assert abs(dcost - gp) <= 1e-6 * abs(gp)
+    prob.close()
