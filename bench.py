@@ -422,7 +422,7 @@ def run_gpu(args):
         dist.destroy_process_group()
 
 
-def batch_leg(rank, world, group, n_per_gpu=64, n_streams=16):
+def batch_leg(rank, world, group, n_per_gpu=64, n_streams=12):
     """BASELINE configs[4] on a bounded sample: n_per_gpu x world independent 4-camera x 1000-frame problems
     (cfg1 shape, one seed each), every one a complete ba_main run (triangulated start, reference tolerances), host
     arrays in and host results out — dealt round-robin over the ranks, n_streams worker streams per GPU.  The

@@ -18,6 +18,20 @@ P_f64 = C.POINTER(C.c_double)
 P_i64 = C.POINTER(C.c_int64)
 P_i32 = C.POINTER(C.c_int32)
 
+TRF_MAX_HIST = 64
+
+
+class TrfState(C.Structure):
+    """bax_trf_state (include/bax.h)."""
+    _fields_ = [("ftol", f64), ("xtol", f64), ("gtol", f64), ("max_nfev", i64),
+                ("x", vp), ("x_new", vp), ("step", vp),
+                ("cost", f64), ("g_inf", f64), ("g_2", f64), ("x_norm", f64), ("h_scale", f64), ("Delta", f64),
+                ("alpha", f64), ("initial_cost", f64),
+                ("nfev", i64), ("njev", i64), ("iteration", i64), ("n_trials", i64),
+                ("status", C.c_int32), ("n_hist", C.c_int32),
+                ("hist", (f64 * 8) * TRF_MAX_HIST)]
+
+
 _SIGS = {
     "bax_last_error": (C.c_char_p, []),
     "bax_version": (i32, []),
@@ -43,6 +57,9 @@ _SIGS = {
     "bax_trial_begin": (i32, [vp, f64, vp]),
     "bax_trial_mid": (i32, [vp, vp, i32, vp]),
     "bax_trial_finish": (i32, [vp, P_f64, vp]),
+    "bax_trf_begin": (i32, [vp, C.POINTER(TrfState), vp]),
+    "bax_trf_iterate": (i32, [vp, C.POINTER(TrfState), vp]),
+    "bax_trf_solve": (i32, [vp, C.POINTER(TrfState), vp]),
     "bax_triangulate": (i32, [vp, vp, vp, vp, P_i32, vp]),
     "bax_reproject_error": (i32, [vp, vp, vp, vp, vp, vp]),
     "bax_timing_enable": (i32, [vp, i32]),

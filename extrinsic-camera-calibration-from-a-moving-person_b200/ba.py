@@ -8,6 +8,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 
 import numpy as np
 import torch
@@ -92,7 +93,7 @@ class BAProblem:
     `group`; the small packed buffers are all-reduced between the kernel phases (include/bax.h)."""
 
     def __init__(self, K, sp2d, ss2d, sp3d, ss3d, bone_idx=OP_BONE, lambda1=1.0, lambda2=1.0,
-                 device=None, group=None, n_frames_global=None):
+                 device=None, group=None, n_frames_global=None, handle=None):
         if not torch.cuda.is_available():
             raise BaxError("no CUDA device: this package has no CPU fallback")
         self.L = lib()
@@ -113,8 +114,11 @@ class BAProblem:
             self.B = int(bones.shape[0])
             self.bones = bones
             self.lambda1, self.lambda2 = float(lambda1), float(lambda2)
-            h = C.c_void_p()
-            check(self.L.bax_create(self.dev.index or 0, C.byref(h)), "bax_create")
+            if handle is not None:                 # a handle detach()ed from a finished problem (sweeps: ba_batch)
+                h = handle
+            else:
+                h = C.c_void_p()
+                check(self.L.bax_create(self.dev.index or 0, C.byref(h)), "bax_create")
             self.h = h
             check(self.L.bax_problem_set(self.h, self.C, self.N, self.J, self.J3, self.B,
                                          self.K.data_ptr(), self.y.data_ptr(), self.s.data_ptr(),
@@ -141,6 +145,12 @@ class BAProblem:
         assert y.numel() == self.y.numel() and s.numel() == self.s.numel() and y.is_contiguous() and s.is_contiguous()
         check(self.L.bax_observations_rebind(self.h, y.data_ptr(), s.data_ptr()), "bax_observations_rebind")
         self.y, self.s = y.reshape(self.C, self.P, 2), s.reshape(self.C, self.P)
+
+    def detach(self):
+        """Give up the libbax handle without destroying it: the next BAProblem(handle=...) on the same device reuses
+        its pinned staging, events and stream-ordered memory (bax_problem_set releases the old problem itself)."""
+        h, self.h = self.h, None
+        return h
 
     def close(self):
         if getattr(self, "h", None):
@@ -450,25 +460,73 @@ class TRFSolver:
     trust-region solves and cost evaluations until a step is accepted (or evaluations run out), then a
     re-linearisation."""
 
-    def __init__(self, prob, theta0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, speculative=True):
+    def __init__(self, prob, theta0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, speculative=True, native=None):
         self.prob = prob
         # speculative: a trial point is linearised straight away (its cost falls out of the linearisation), so an
         # accepted step needs no separate cost pass; a rejected step restores the saved linearisation
         self.speculative = speculative
+        # native: the same loop behind one C-ABI call per outer iteration (csrc/bax_trf.cu) — one GPU only; a
+        # frame-sharded run all-reduces between the phases and stays in this class's Python statements
+        if native is None:
+            native = os.environ.get("BAX_TRF_HOST", "0") != "1"
+        self.native = bool(native) and speculative and prob.group is None
         self.x = prob._dev_theta(theta0).clone()
         self.x_new = torch.empty_like(self.x)
         self.ftol, self.xtol, self.gtol = ftol, xtol, gtol
+        self.max_nfev = 100 * prob.n if max_nfev is None else max_nfev
+        self.history = []
+        if self.native:
+            st = self._st = _lib.TrfState()
+            st.ftol, st.xtol, st.gtol, st.max_nfev = ftol, xtol, gtol, int(self.max_nfev)
+            st.x, st.x_new, st.step = self.x.data_ptr(), self.x_new.data_ptr(), prob.step.data_ptr()
+            with torch.cuda.device(prob.dev):
+                rc = prob.L.bax_trf_begin(prob.h, C.byref(st), _stream())
+            if rc != 0 and not math.isfinite(st.cost):
+                raise ValueError("Residuals are not finite in the initial point.")
+            check(rc, "bax_trf_begin")
+            self._pull()
+            return
         self.cost, self.g_inf, self.g_2, self.x_norm = prob.linearize(self.x)
         if not math.isfinite(self.cost):
             raise ValueError("Residuals are not finite in the initial point.")
         self.initial_cost = self.cost
         self.nfev, self.njev = 1, 1
-        self.max_nfev = 100 * prob.n if max_nfev is None else max_nfev
         self.Delta = self.x_norm if self.x_norm > 0 else 1.0
         self.alpha = 0.0
         self.status = None
         self.iteration = 0
-        self.history = []
+
+    # ---- native state <-> attributes (the attributes stay the interface: bench.py and the tests set Delta / alpha)
+    def _pull(self):
+        st = self._st
+        self.cost, self.g_inf, self.g_2, self.x_norm = st.cost, st.g_inf, st.g_2, st.x_norm
+        self.initial_cost, self.Delta, self.alpha = st.initial_cost, st.Delta, st.alpha
+        self.nfev, self.njev, self.iteration = int(st.nfev), int(st.njev), int(st.iteration)
+        self.status = None if st.status < 0 else int(st.status)
+        self.prob.h_scale = st.h_scale
+        if st.x != self.x.data_ptr():                      # an accepted step swapped the roles of the two vectors
+            self.x, self.x_new = self.x_new, self.x
+        self.prob._keep_lin = self.x
+
+    def _push(self):
+        st = self._st
+        st.cost, st.g_inf, st.g_2, st.x_norm, st.h_scale = self.cost, self.g_inf, self.g_2, self.x_norm, self.prob.h_scale
+        st.Delta, st.alpha = self.Delta, self.alpha
+        st.nfev, st.njev, st.iteration = self.nfev, self.njev, self.iteration
+        st.status = -1 if self.status is None else self.status
+        st.x, st.x_new = self.x.data_ptr(), self.x_new.data_ptr()
+
+    def _iterate_native(self):
+        st, prob = self._st, self.prob
+        self._push()
+        n0 = int(st.n_trials)
+        with torch.cuda.device(prob.dev):
+            check(prob.L.bax_trf_iterate(prob.h, C.byref(st), _stream()), "bax_trf_iterate")
+        prob.n_trials += int(st.n_trials) - n0
+        for k in range(st.n_hist):
+            r = st.hist[k]
+            self.history.append(dict(alpha=r[0], Delta=r[1], step_norm=r[2], cost_new=r[3], pred=r[4], act=r[5], n_it=int(r[6])))
+        self._pull()
 
     def done(self):
         if self.status is None and self.g_inf < self.gtol:
@@ -476,6 +534,8 @@ class TRFSolver:
         return self.status is not None or self.nfev >= self.max_nfev
 
     def iterate(self, relinearize=True):
+        if self.native and relinearize:
+            return self._iterate_native()
         prob = self.prob
         actual_reduction = -1.0
         cost_new = self.cost
@@ -524,6 +584,16 @@ class TRFSolver:
                 self.cost = cost_new
         self.iteration += 1
 
+    def solve_native(self):
+        """All remaining iterations behind ONE call across the ABI (bax_trf_iterate until termination, in C)."""
+        st, prob = self._st, self.prob
+        self._push()
+        n0 = int(st.n_trials)
+        with torch.cuda.device(prob.dev):
+            check(prob.L.bax_trf_solve(prob.h, C.byref(st), _stream()), "bax_trf_solve")
+        prob.n_trials += int(st.n_trials) - n0
+        self._pull()
+
     def result(self):
         status = 0 if self.status is None else self.status
         return dict(x=self.x, cost=self.cost, optimality=self.g_inf, nfev=self.nfev, njev=self.njev,
@@ -534,6 +604,8 @@ class TRFSolver:
 def trf_schur(prob, theta0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, verbose=0, callback=None):
     """Run TRFSolver to termination.  Returns a dict like SciPy's OptimizeResult (x stays on the device)."""
     sol = TRFSolver(prob, theta0, ftol, xtol, gtol, max_nfev)
+    if sol.native and callback is None:
+        sol.solve_native()
     while not sol.done():
         sol.iterate()
         if callback is not None:
@@ -576,12 +648,13 @@ def jacobian(params, K, sp2d, ss2d, sp3d, ss3d, bone_idx, C, N, J, lambda1, lamb
 
 
 def ba_main(camid, K, R_w2c, t_w2c, sp2d, ss2d, sp3d, ss3d, lambda1, lambda2, *,
-            ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, verbose=True, return_info=False):
+            ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, verbose=True, return_info=False, _reuse=None):
     """Drop-in for reference ba.ba_main (ba.py:157-210): triangulate the start, print the three initial
     mean costs, minimise ba.objfun by trust-region least squares (ftol=1e-4), unpack."""
     C = len(camid)
     N, J = sp2d.shape[1], sp2d.shape[2]
-    prob = BAProblem(K, np.asarray(sp2d).reshape(C, N * J, 2), ss2d, sp3d, ss3d, OP_BONE, lambda1, lambda2)
+    prob = BAProblem(K, np.asarray(sp2d).reshape(C, N * J, 2), ss2d, sp3d, ss3d, OP_BONE, lambda1, lambda2,
+                     handle=_reuse.pop("h", None) if _reuse is not None else None)
     try:
         x_all = prob.triangulate(R_w2c, t_w2c).reshape(N * J, 3)
         theta0 = to_theta(R_w2c, t_w2c, x_all)
@@ -600,7 +673,10 @@ def ba_main(camid, K, R_w2c, t_w2c, sp2d, ss2d, sp3d, ss3d, lambda1, lambda2, *,
         theta = res["x"].cpu().numpy()
         res["x"] = theta
     finally:
-        prob.close()
+        if _reuse is not None:
+            _reuse["h"] = prob.detach()         # the sweep's worker keeps the handle for its next problem
+        else:
+            prob.close()
     R, t, x = from_theta(theta, C)
     return (R, t, x, res) if return_info else (R, t, x)
 
@@ -614,13 +690,25 @@ def batch_plan(n_problems, rank=0, world=1):
     return list(range(rank, n_problems, world))
 
 
-def ba_batch(problems, lambda1, lambda2, *, n_streams=16, group=None, gather=True, solve=None, **kw):
+_worker_streams = {}
+
+
+def _worker_stream(dev, i):
+    """The i-th worker stream of device `dev`, created once per process: torch's caching allocator keeps its blocks
+    per stream, so a sweep that came back with fresh streams would pay cudaMalloc for its uploads again."""
+    pool = _worker_streams.setdefault(dev, [])
+    while len(pool) <= i:
+        pool.append(torch.cuda.Stream(device=dev))
+    return pool[i]
+
+
+def ba_batch(problems, lambda1, lambda2, *, n_streams=12, group=None, gather=True, solve=None, **kw):
     """Multi-sequence sweep: `ba_main` on every entry of `problems` — a sequence of
     (camid, K, R_w2c, t_w2c, sp2d, ss2d, sp3d, ss3d) tuples (or callables returning one, so a sweep need not
     hold every scene in host memory) — each by the same code path and therefore with the same result as a
     single `ba_main` call.
 
-    One GPU: `n_streams` worker threads, each with its own CUDA stream and its own libbax handle, pull problem
+    One GPU: `n_streams` worker threads, each with its own (persistent) CUDA stream and its own libbax handle, pull problem
     indices from a shared queue.  A 4-camera problem is launch- and latency-bound on its own (a few hundred CTAs
     per kernel, ~40 launches and 2-3 scalar read-backs per trust-region iteration); the streams overlap the
     kernels of one problem with the read-backs and host logic of the others.  ctypes releases the GIL for the
@@ -647,11 +735,15 @@ def ba_batch(problems, lambda1, lambda2, *, n_streams=16, group=None, gather=Tru
     for k in mine:
         q.put(k)
 
-    def worker():
+    def worker(i=0):
         cuda = torch.cuda.is_available()
-        ctx = torch.cuda.stream(torch.cuda.Stream()) if cuda else None
+        ctx = torch.cuda.stream(_worker_stream(torch.cuda.current_device(), i)) if cuda else None
         if ctx is not None:
             ctx.__enter__()
+        extra = dict(kw)
+        reuse = {}
+        if solve is ba_main:
+            extra["_reuse"] = reuse             # one libbax handle per worker, re-bound to each problem in turn
         try:
             while not errors:
                 try:
@@ -659,10 +751,12 @@ def ba_batch(problems, lambda1, lambda2, *, n_streams=16, group=None, gather=Tru
                 except queue.Empty:
                     return
                 p = problems[k]() if callable(problems[k]) else problems[k]
-                results[k] = solve(*p, lambda1, lambda2, **kw)
+                results[k] = solve(*p, lambda1, lambda2, **extra)
         except BaseException as e:          # surfaced by the caller, with the failing problem's index
             errors.append((k, e))
         finally:
+            if reuse.get("h") is not None:
+                lib().bax_destroy(reuse.pop("h"))
             if ctx is not None:
                 ctx.__exit__(None, None, None)
 
@@ -672,11 +766,11 @@ def ba_batch(problems, lambda1, lambda2, *, n_streams=16, group=None, gather=Tru
     else:
         dev = torch.cuda.current_device() if torch.cuda.is_available() else None
 
-        def entry():
+        def entry(i):
             if dev is not None:
                 torch.cuda.set_device(dev)
-            worker()
-        threads = [threading.Thread(target=entry, name=f"ba_batch-{i}") for i in range(n_thr)]
+            worker(i)
+        threads = [threading.Thread(target=entry, args=(i,), name=f"ba_batch-{i}") for i in range(n_thr)]
         for t in threads:
             t.start()
         for t in threads:

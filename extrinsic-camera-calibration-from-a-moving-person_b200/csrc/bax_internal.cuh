@@ -72,6 +72,7 @@ struct bax_handle {
   size_t syrk_part_bytes;
   double* dense_ws;          // S factor (6C x 6C), Z (B x 6C), LT (B x B), pc, w, misc
   double* coef;              // [6C + B] coefficients for back-substitution
+  double* lin_stage;         // [<= 4096] scalars of a linearisation gathered for one device -> host copy
   // ---- reduce buffers (see bax_reduce_buffer)
   double* buf[8];
   int64_t buf_count[8];

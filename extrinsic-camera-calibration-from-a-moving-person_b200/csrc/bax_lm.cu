@@ -389,18 +389,32 @@ extern "C" int bax_linearize_post(bax_handle* h, void* stream) {
   return BAX_OK;
 }
 
+// scalars of a linearisation gathered into one contiguous block (layout of bax_linearize_finish's staging area)
+__global__ void k_lin_stage(const double* __restrict__ lin_tail, const double* __restrict__ norm, const double* __restrict__ gmax,
+                            const double* __restrict__ bone_n, const double* __restrict__ theta, int C6, int B,
+                            double* __restrict__ out) {
+  const int n1 = C6 + B + 2;
+  for (int i = threadIdx.x; i < n1; i += blockDim.x) out[i] = lin_tail[i];
+  for (int i = threadIdx.x; i < C6; i += blockDim.x) out[n1 + 6 + i] = theta[i];
+  if (threadIdx.x == 0) {
+    out[n1] = norm[0]; out[n1 + 1] = norm[1]; out[n1 + 2] = gmax[0]; out[n1 + 3] = *bone_n; out[n1 + 4] = gmax[1];
+    out[n1 + 5] = 0.0;
+  }
+}
+
 extern "C" int bax_linearize_finish(bax_handle* h, double* out_host, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
   const int C6 = 6 * h->C, B = h->B;
   if (C6 + B + 2 + 8 + C6 > 4096) { bax_set_error("too many cameras for the scalar staging buffer"); return BAX_E_ARG; }
-  static thread_local double stage[4096];
+  // one gather kernel + one copy into pinned memory instead of six small pageable copies (each of those is a
+  // separate driver round trip: ~40 us per linearisation, which a 4-camera problem feels)
+  const int n_stage = C6 + B + 8 + C6;
   double* lin = h->buf[BAX_BUF_LIN];
-  BAX_CUDA(cudaMemcpyAsync(stage, lin + (size_t)C6 * C6, sizeof(double) * (C6 + B + 2), cudaMemcpyDeviceToHost, s));
-  BAX_CUDA(cudaMemcpyAsync(stage + C6 + B + 2, h->buf[BAX_BUF_NORM], sizeof(double) * 2, cudaMemcpyDeviceToHost, s));
-  BAX_CUDA(cudaMemcpyAsync(stage + C6 + B + 4, h->buf[BAX_BUF_GMAX], sizeof(double), cudaMemcpyDeviceToHost, s));
-  BAX_CUDA(cudaMemcpyAsync(stage + C6 + B + 6, h->buf[BAX_BUF_GMAX] + 1, sizeof(double), cudaMemcpyDeviceToHost, s));
-  BAX_CUDA(cudaMemcpyAsync(stage + C6 + B + 5, h->buf[BAX_BUF_BONE] + B, sizeof(double), cudaMemcpyDeviceToHost, s));
-  BAX_CUDA(cudaMemcpyAsync(stage + C6 + B + 8, h->theta_lin, sizeof(double) * C6, cudaMemcpyDeviceToHost, s));
+  k_lin_stage<<<1, 256, 0, s>>>(lin + (size_t)C6 * C6, h->buf[BAX_BUF_NORM], h->buf[BAX_BUF_GMAX], h->buf[BAX_BUF_BONE] + B,
+                                h->theta_lin, C6, B, h->lin_stage);
+  BAX_LAUNCH_CHECK();
+  double* stage = h->host_pinned + 64;
+  BAX_CUDA(cudaMemcpyAsync(stage, h->lin_stage, sizeof(double) * n_stage, cudaMemcpyDeviceToHost, s));
   BAX_CUDA(cudaStreamSynchronize(s));
   const double* gc = stage; const double* ssq = stage + C6;
   double ginf = stage[C6 + B + 4], g2 = stage[C6 + B + 2], x2 = stage[C6 + B + 3];

@@ -140,14 +140,12 @@ extern "C" int bax_create(int device, bax_handle** out) {
   BAX_CUDA(cudaSetDevice(device));
   bax_handle* h = (bax_handle*)calloc(1, sizeof(bax_handle));
   h->device = device;
-  cudaDeviceProp prop;
-  BAX_CUDA(cudaGetDeviceProperties(&prop, device));
-  h->sm_count = prop.multiProcessorCount;
+  BAX_CUDA(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device));   // (cudaGetDeviceProperties costs ~1 ms)
   { const char* e = getenv("BAX_DENSE_COOP"); h->dense_coop = e ? atoi(e) : 1; }
   { const char* e = getenv("BAX_RJ_VARIANT"); h->rj_variant = e ? atoi(e) : -1; }
   BAX_CUDA(cudaEventCreate(&h->ev0));
   BAX_CUDA(cudaEventCreate(&h->ev1));
-  BAX_CUDA(cudaMallocHost((void**)&h->host_pinned, 64 * sizeof(double)));
+  BAX_CUDA(cudaMallocHost((void**)&h->host_pinned, (64 + 4096) * sizeof(double)));   // [0,64): trial scalars; [64,..): linearisation scalars
   {  // freed blocks stay in the device's default pool: the next handle of a sweep gets them back without a driver call
     cudaMemPool_t pool; unsigned long long keep = ~0ULL;
     if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
@@ -167,13 +165,13 @@ void bax_dev_free(bax_handle* h, void* p) {
 
 static void free_problem(bax_handle* h) {
   void* ptrs[] = {(void*)h->K, h->bones, h->joint_bones, h->dhat, h->blockbase, h->campack, h->campack_lin, h->Vp, h->gp,
-                  h->Hcc, h->gc, h->Lbar, h->rb, h->Yhat, h->Gv, h->syrk_part, h->dense_ws, h->coef,
+                  h->Hcc, h->gc, h->Lbar, h->rb, h->lin_stage, h->Yhat, h->Gv, h->syrk_part, h->dense_ws, h->coef,
                   h->partials, h->saved.Vp, h->saved.gp, h->saved.lin, h->saved.Lbar, h->saved.rb, h->saved.campack_lin};
   for (void* p : ptrs) bax_dev_free(h, p);
   for (int i = 0; i < 8; ++i) { bax_dev_free(h, h->buf[i]); h->buf[i] = nullptr; }
   h->K = nullptr; h->bones = nullptr; h->joint_bones = nullptr; h->dhat = nullptr; h->blockbase = nullptr;
   h->campack = nullptr; h->campack_lin = nullptr; h->Vp = h->gp = h->Hcc = h->gc = h->Lbar = h->rb = nullptr;
-  h->Yhat = h->Gv = h->syrk_part = h->dense_ws = h->coef = h->partials = nullptr;
+  h->Yhat = h->Gv = h->syrk_part = h->dense_ws = h->coef = h->partials = h->lin_stage = nullptr;
   h->saved.Vp = h->saved.gp = h->saved.lin = h->saved.Lbar = h->saved.rb = h->saved.campack_lin = nullptr; h->saved.valid = 0;
   h->syrk_part_bytes = 0;
 }
@@ -287,6 +285,7 @@ extern "C" int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B
   BAX_CUDA(cudaMemsetAsync(h->Lbar, 0, sizeof(double) * BAX_MAX_B, s));
   BAX_CUDA(cudaMemsetAsync(h->rb, 0, sizeof(double) * BAX_MAX_B, s));
   BAX_ALLOC(h, h->coef, sizeof(double) * (C6 + BAX_MAX_B));
+  BAX_ALLOC(h, h->lin_stage, sizeof(double) * 4096);
   BAX_ALLOC(h, h->dense_ws, sizeof(double) * ((size_t)C6 * C6 + (size_t)BAX_MAX_B * C6 * 2 + 4 * C6 + 1024));
   h->partials_bytes = sizeof(double) * (size_t)(1 << 22);
   BAX_ALLOC(h, h->partials, h->partials_bytes);

@@ -105,6 +105,28 @@ int bax_trial_begin(bax_handle* h, double alpha, void* stream);
 int bax_trial_mid(bax_handle* h, double* step, int need_phi_prime, void* stream);
 int bax_trial_finish(bax_handle* h, double* out_host, void* stream);
 
+/* ---- whole trust-region iterations behind one call (one GPU; a frame-sharded run all-reduces between the phases
+ * above and is driven from the host language instead).  Same scalar logic as SciPy's trf_no_bounds
+ * (scipy/optimize/_lsq/trf.py:415-587 — what reference ba.py:187-206 runs) with x_scale = 1: Delta_0 = ||x_0||,
+ * More'-Sorensen alpha iteration, boundary-step rescaling, update_tr_radius, check_termination; every trial point
+ * is linearised straight away (bax_linearize_push / _pop).  The caller fills the options and the three device
+ * vectors (n doubles each; x holds the start) and keeps the struct alive between calls; x and x_new swap roles on
+ * accepted steps, so the solution is wherever st->x points afterwards. */
+#define BAX_TRF_MAX_HIST 64
+typedef struct bax_trf_state {
+  double ftol, xtol, gtol;        /* SciPy defaults of the reference call: 1e-4 (ba.py:190), 1e-8, 1e-8 */
+  int64_t max_nfev;               /* <= 0: 100 * n (SciPy's default for trf) */
+  double *x, *x_new, *step;       /* device, n doubles each */
+  double cost, g_inf, g_2, x_norm, h_scale, Delta, alpha, initial_cost;
+  int64_t nfev, njev, iteration, n_trials;
+  int32_t status;                 /* -1 while running, else SciPy's status 0..4 */
+  int32_t n_hist;                 /* inner passes recorded by the last bax_trf_iterate */
+  double hist[BAX_TRF_MAX_HIST][8]; /* alpha, Delta, step norm, cost at the trial point, predicted, actual, More' its, accepted */
+} bax_trf_state;
+int bax_trf_begin(bax_handle* h, bax_trf_state* st, void* stream);    /* linearises at st->x, sets Delta_0 */
+int bax_trf_iterate(bax_handle* h, bax_trf_state* st, void* stream);  /* one pass of the outer loop body */
+int bax_trf_solve(bax_handle* h, bax_trf_state* st, void* stream);    /* after begin: iterate until termination; hist = last pass */
+
 /* Weighted linear triangulation of every (frame, joint) — util.triangulate_with_conf,
  * reference util.py:325-354 (+ triangulate_point 308-322).  R [C][9], t [C][3]; X [N*J][3] (NaN where
  * the reference returns NaN); status_host: 0 ok, 1 = some point has rank < 3 ("not enough constraint"). */

@@ -415,3 +415,31 @@ def test_full_size_configs_vs_oracle_and_step_identity(which):
     dcost = (prob.cost(thd + eps * p) - prob.cost(thd - eps * p)) / (2 * eps)
     assert abs(dcost - gp) <= 1e-6 * abs(gp)
     prob.close()
+
+
+@pytest.mark.parametrize("case", ["small", "partial", "gafa_lambda"])
+def test_native_trust_region_driver_same_path(golden_dir, case):
+    """The C-side driver (bax_trf_begin / _iterate / _solve, csrc/bax_trf.cu) and the Python statements of TRFSolver
+    are the same algorithm: identical (alpha, Delta, step norm, cost, predicted, actual, More' iterations) sequence,
+    rejected steps included, identical end point; bax_trf_solve in one call lands on the same point."""
+    g, args, prob = _load(golden_dir, case)
+    runs = []
+    for native in (False, True):
+        sol = ba.TRFSolver(prob, g["theta0"], ftol=1e-10, xtol=1e-12, gtol=1e-12, max_nfev=25, native=native)
+        assert sol.native == native
+        while not sol.done():
+            sol.iterate()
+        runs.append((sol.history, sol.x.cpu().numpy().copy(), sol.nfev, sol.njev, sol.status, sol.cost))
+    (h0, x0, nf0, nj0, s0, c0), (h1, x1, nf1, nj1, s1, c1) = runs
+    assert (nf0, nj0, s0) == (nf1, nj1, s1) and len(h0) == len(h1) and len(h0) >= 3
+    for a, b in zip(h0, h1):
+        for k in ("alpha", "Delta", "step_norm", "cost_new", "pred", "act"):
+            assert abs(a[k] - b[k]) <= 1e-12 * max(abs(a[k]), 1e-300), (k, a[k], b[k])
+        assert a["n_it"] == b["n_it"]
+    assert np.max(np.abs(x0 - x1)) <= 1e-13 * np.max(np.abs(x0)) and abs(c0 - c1) <= 1e-13 * c0
+    sol = ba.TRFSolver(prob, g["theta0"], ftol=1e-10, xtol=1e-12, gtol=1e-12, max_nfev=25, native=True)
+    sol.solve_native()
+    assert sol.done() and sol.nfev == nf1 and np.array_equal(sol.x.cpu().numpy(), x1)
+    res = sol.result()
+    assert res["status"] == (0 if s1 is None else s1) and res["njev"] == nj1
+    prob.close()
