@@ -135,7 +135,8 @@ extern "C" int bax_cost_finish(bax_handle* h, double* cost_host, void* stream) {
 
 // ------------------------------------------------------------------ linearisation
 // per-camera 6x6 block sum_p Jc^T Jc (21 unique), gradient Jc^T e (6), sum e^2 (1).
-__global__ void __launch_bounds__(256)
+template <int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB)
 k_lin_cam(const double* __restrict__ campack, const double* __restrict__ x, const double2* __restrict__ y,
           const double* __restrict__ s, int64_t P, int C, double* __restrict__ part /*[gridDim.x][C][28]*/) {
   __shared__ double cam[CAMPACK];
@@ -146,7 +147,7 @@ k_lin_cam(const double* __restrict__ campack, const double* __restrict__ x, cons
   double acc[28];
 #pragma unroll
   for (int i = 0; i < 28; ++i) acc[i] = 0.0;
-  for (int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x; p < P; p += (int64_t)gridDim.x * 256) {
+  for (int64_t p = (int64_t)blockIdx.x * NT + threadIdx.x; p < P; p += (int64_t)gridDim.x * NT) {
     double sc = s[(size_t)c * P + p];
     if (sc > 0) {
       double2 yy = y[(size_t)c * P + p];
@@ -169,6 +170,80 @@ k_lin_cam(const double* __restrict__ campack, const double* __restrict__ x, cons
   if (threadIdx.x == 0) {
     double* o = part + ((size_t)blockIdx.x * C + c) * 28;
     for (int i = 0; i < 28; ++i) o[i] = acc[i];
+  }
+}
+
+// The same 28 sums on the FP64 tensor pipe.  With A_c = [J_c | e] (two rows of 7 per observation) the camera block,
+// the gradient and the cost are the 7 x 7 matrix A_c^T A_c — a SYRK with 8 (7 used) rows and K = 2 x visible
+// observations.  Each lane linearises one observation and parks its 2 x 8 values in the warp's shared-memory slab
+// X[col][k] (k = 2 lane + row; column stride 68 doubles: the 16-byte stores are contiguous across lanes, the operand
+// loads X[lane>>2][4 kk + (lane&3)] hit every bank pair once); 16 mma.sync.m8n8k4.f64 then fold the 64 K-rows into the
+// warp's 8 x 8 accumulator tile, both operands being the same element (C += X^T X).  Two accumulator registers per
+// lane instead of 28: the kernel needs 70-odd registers where the DFMA version needs 166 (one CTA of 8 warps per SM),
+// and the 28-value block reduction disappears.
+#define LCM_WARPS 4
+#define LCM_LD 68
+__device__ __forceinline__ void lcm_dmma(double (&c)[2], double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+               : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
+__global__ void __launch_bounds__(32 * LCM_WARPS, 4)
+k_lin_cam_mma(const double* __restrict__ campack, const double* __restrict__ x, const double2* __restrict__ y,
+              const double* __restrict__ s, int64_t P, int C, double* __restrict__ part /*[gridDim.x][C][28]*/) {
+  __shared__ double cam[CAMPACK];
+  __shared__ __align__(16) double X[LCM_WARPS][8 * LCM_LD];
+  const int c = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x < CAMPACK) cam[threadIdx.x] = campack[(size_t)c * CAMPACK + threadIdx.x];
+  __syncthreads();
+  double acc[2] = {0.0, 0.0};
+  double* Xw = X[warp];
+  const int NT = 32 * LCM_WARPS;
+  // every lane of a warp runs the same number of rounds (the DMMA is warp-wide); out-of-range lanes contribute zeros
+  const int64_t stride = (int64_t)gridDim.x * NT;
+  for (int64_t base = (int64_t)blockIdx.x * NT + warp * 32; base < P; base += stride) {
+    const int64_t p = base + lane;
+    double j0[8] = {0, 0, 0, 0, 0, 0, 0, 0}, j1[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (p < P) {
+      const double sc = s[(size_t)c * P + p];
+      if (sc > 0) {
+        const double2 yy = y[(size_t)c * P + p];
+        ObsLin o;
+        obs_linearize<true>(cam, x[3 * p], x[3 * p + 1], x[3 * p + 2], yy.x, yy.y, sc, o);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { j0[k] = o.jr[0][k]; j0[3 + k] = o.jt[0][k]; j1[k] = o.jr[1][k]; j1[3 + k] = o.jt[1][k]; }
+        j0[6] = o.e0; j1[6] = o.e1;
+      }
+    }
+#pragma unroll
+    for (int col = 0; col < 8; ++col)
+      *reinterpret_cast<double2*>(Xw + col * LCM_LD + 2 * lane) = make_double2(j0[col], j1[col]);
+    __syncwarp();
+    const double* src = Xw + (lane >> 2) * LCM_LD + (lane & 3);
+#pragma unroll
+    for (int kk = 0; kk < 16; ++kk) {
+      const double v = src[4 * kk];
+      lcm_dmma(acc, v, v);
+    }
+    __syncwarp();
+  }
+  // acc = C[lane>>2][2 (lane&3) + {0,1}] of this warp; fixed-order sum over the warps, then the packed 28 values
+  __syncthreads();
+  double* red = &X[0][0];                       // [LCM_WARPS][64]
+  red[warp * 64 + (lane >> 2) * 8 + 2 * (lane & 3)] = acc[0];
+  red[warp * 64 + (lane >> 2) * 8 + 2 * (lane & 3) + 1] = acc[1];
+  __syncthreads();
+  if (threadIdx.x < 28) {
+    int a, b;
+    if (threadIdx.x < 21) {                     // k-th entry of the upper triangle of the 6 x 6 block, row-major
+      int k = threadIdx.x; a = 0;
+      while (k >= 6 - a) { k -= 6 - a; ++a; }
+      b = a + k;
+    } else if (threadIdx.x < 27) { a = threadIdx.x - 21; b = 6; }
+    else { a = 6; b = 6; }
+    double v = 0.0;
+#pragma unroll
+    for (int w = 0; w < LCM_WARPS; ++w) v += red[w * 64 + a * 8 + b];
+    part[((size_t)blockIdx.x * C + c) * 28 + threadIdx.x] = v;
   }
 }
 
@@ -341,7 +416,18 @@ extern "C" int bax_linearize_mid(bax_handle* h, void* stream) {
     int g = obs_grid(h);
     double* part = h->partials;                  // [g][C][28]
     if ((size_t)g * C * 28 * sizeof(double) > h->partials_bytes / 4) { bax_set_error("partials overflow"); return BAX_E_STATE; }
-    k_lin_cam<<<dim3(g, C), 256, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
+    // BAX_LINCAM: tuning knob — 4 (default) = DMMA kernel; 0..3 = DFMA kernel at 256x1, 128x3, 256x2, 128x4 CTAs/SM
+    static const int lc_variant = getenv("BAX_LINCAM") ? atoi(getenv("BAX_LINCAM")) : 4;
+    if (lc_variant >= 4) {                       // one wave of 4 resident CTAs per SM
+      int gm = (4 * h->sm_count) / C; if (gm < 1) gm = 1;
+      int nb128 = (int)((h->P + 127) / 128);
+      g = gm < nb128 ? gm : nb128;
+    }
+    if (lc_variant == 0) k_lin_cam<256, 1><<<dim3(g, C), 256, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
+    else if (lc_variant == 1) k_lin_cam<128, 3><<<dim3(g, C), 128, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
+    else if (lc_variant == 2) k_lin_cam<256, 2><<<dim3(g, C), 256, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
+    else if (lc_variant == 3) k_lin_cam<128, 4><<<dim3(g, C), 128, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
+    else k_lin_cam_mma<<<dim3(g, C), 32 * LCM_WARPS, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
     BAX_LAUNCH_CHECK();
     double* camsum = h->partials + (1 << 20);    // [C][28]
     rc = bax_reduce_partials(h, part, g, C * 28, camsum, s); if (rc) return rc;
