@@ -59,10 +59,22 @@ k_build_yhat(const double* __restrict__ campack, const double* __restrict__ x, c
       }
     }
   }
+  // the (score, 2-D point) of the cameras two and one iterations ahead are in flight while this one is worked on:
+  // a score-then-point load chain per camera left the kernel waiting on memory (ncu: long_scoreboard on top)
+  double sc_q[2]; double2 yy_q[2];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int cc = k < C ? k : C - 1;
+    sc_q[k] = s[(size_t)cc * P + p]; yy_q[k] = y[(size_t)cc * P + p];
+  }
+#pragma unroll 2
   for (int c = 0; c < C; ++c) {
-    double sc = s[(size_t)c * P + p];
+    const double sc = sc_q[c & 1]; const double2 yy = yy_q[c & 1];
+    {
+      const int cn = c + 2 < C ? c + 2 : C - 1;
+      sc_q[c & 1] = s[(size_t)cn * P + p]; yy_q[c & 1] = y[(size_t)cn * P + p];
+    }
     if (!(sc > 0)) continue;                     // rows of unseen cameras stay zero (buffer is zero-initialised)
-    double2 yy = y[(size_t)c * P + p];
     ObsLin o;
     obs_linearize<true>(cams + c * CAMPACK, x0, x1, x2, yy.x, yy.y, sc, o);
 #pragma unroll
