@@ -8,6 +8,9 @@
 
 #define BAX_MAX_B 16          // bones (reference: 12, util.py:129-145)
 #define BAX_MAX_JB 4          // bones incident to one joint (reference skeleton: <= 3)
+#ifndef BAX_PF
+#define BAX_PF 2              // cameras whose (score, 2-D point) loads are in flight ahead of the one worked on (4 measured no faster)
+#endif
 #define CAMPACK 48            // doubles per camera staged in shared memory (padded to 16 B multiples)
 // CamPack layout: K[0..8] R[9..17] t[18..20] M[21..29] Mn[30..38]   (M, Mn: see k_cam_prep)
 

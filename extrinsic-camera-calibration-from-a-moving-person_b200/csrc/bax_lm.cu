@@ -268,18 +268,21 @@ k_lin_pt(const double* __restrict__ campack, const double* __restrict__ x, const
   if (p >= P) return;
   double x0 = x[3 * p], x1 = x[3 * p + 1], x2 = x[3 * p + 2];
   double V[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
-  double sc_q[2]; double2 yy_q[2];               // loads of the next two cameras in flight (see k_build_yhat)
+  double sc_q[BAX_PF]; double2 yy_q[BAX_PF];               // loads of the next BAX_PF cameras in flight (see k_build_yhat)
 #pragma unroll
-  for (int k = 0; k < 2; ++k) {
+  for (int k = 0; k < BAX_PF; ++k) {
     const int cc = k < C ? k : C - 1;
     sc_q[k] = s[(size_t)cc * P + p]; yy_q[k] = y[(size_t)cc * P + p];
   }
-#pragma unroll 2
-  for (int c = 0; c < C; ++c) {
-    const double sc = sc_q[c & 1]; const double2 yy = yy_q[c & 1];
+  for (int c0 = 0; c0 < C; c0 += BAX_PF) {
+#pragma unroll
+   for (int k = 0; k < BAX_PF; ++k) {           // ring slot k is a compile-time index: the queue stays in registers
+    const int c = c0 + k;
+    if (c >= C) break;
+    const double sc = sc_q[k]; const double2 yy = yy_q[k];
     {
-      const int cn = c + 2 < C ? c + 2 : C - 1;
-      sc_q[c & 1] = s[(size_t)cn * P + p]; yy_q[c & 1] = y[(size_t)cn * P + p];
+      const int cn = c + BAX_PF < C ? c + BAX_PF : C - 1;
+      sc_q[k] = s[(size_t)cn * P + p]; yy_q[k] = y[(size_t)cn * P + p];
     }
     if (sc > 0) {
       ObsLin o;
@@ -291,8 +294,9 @@ k_lin_pt(const double* __restrict__ campack, const double* __restrict__ x, const
       V[4] += o.jp[0][1] * o.jp[0][2] + o.jp[1][1] * o.jp[1][2];
       V[5] += o.jp[0][2] * o.jp[0][2] + o.jp[1][2] * o.jp[1][2];
 #pragma unroll
-      for (int k = 0; k < 3; ++k) g[k] += o.jp[0][k] * o.e0 + o.jp[1][k] * o.e1;
+      for (int q = 0; q < 3; ++q) g[q] += o.jp[0][q] * o.e0 + o.jp[1][q] * o.e1;
     }
+   }
   }
 #pragma unroll
   for (int k = 0; k < 6; ++k) Vp[6 * p + k] = V[k];

@@ -59,20 +59,23 @@ k_build_yhat(const double* __restrict__ campack, const double* __restrict__ x, c
       }
     }
   }
-  // the (score, 2-D point) of the cameras two and one iterations ahead are in flight while this one is worked on:
+  // the (score, 2-D point) of the next BAX_PF cameras are in flight while this one is worked on:
   // a score-then-point load chain per camera left the kernel waiting on memory (ncu: long_scoreboard on top)
-  double sc_q[2]; double2 yy_q[2];
+  double sc_q[BAX_PF]; double2 yy_q[BAX_PF];
 #pragma unroll
-  for (int k = 0; k < 2; ++k) {
+  for (int k = 0; k < BAX_PF; ++k) {
     const int cc = k < C ? k : C - 1;
     sc_q[k] = s[(size_t)cc * P + p]; yy_q[k] = y[(size_t)cc * P + p];
   }
-#pragma unroll 2
-  for (int c = 0; c < C; ++c) {
-    const double sc = sc_q[c & 1]; const double2 yy = yy_q[c & 1];
+  for (int c0 = 0; c0 < C; c0 += BAX_PF) {
+#pragma unroll
+   for (int k = 0; k < BAX_PF; ++k) {           // ring slot k is a compile-time index: the queue stays in registers
+    const int c = c0 + k;
+    if (c >= C) break;
+    const double sc = sc_q[k]; const double2 yy = yy_q[k];
     {
-      const int cn = c + 2 < C ? c + 2 : C - 1;
-      sc_q[c & 1] = s[(size_t)cn * P + p]; yy_q[c & 1] = y[(size_t)cn * P + p];
+      const int cn = c + BAX_PF < C ? c + BAX_PF : C - 1;
+      sc_q[k] = s[(size_t)cn * P + p]; yy_q[k] = y[(size_t)cn * P + p];
     }
     if (!(sc > 0)) continue;                     // rows of unseen cameras stay zero (buffer is zero-initialised)
     ObsLin o;
@@ -88,6 +91,7 @@ k_build_yhat(const double* __restrict__ campack, const double* __restrict__ x, c
       double* q = col + (size_t)(6 * c + i) * ldy;
       q[0] = w0; q[1] = w1; q[2] = w2;
     }
+   }
   }
 }
 
