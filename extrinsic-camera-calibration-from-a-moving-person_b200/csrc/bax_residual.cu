@@ -67,7 +67,7 @@ k_rj(const double* __restrict__ campack, const double* __restrict__ x, const dou
   const int64_t row0 = blockbase[(size_t)c * gridDim.x + blockIdx.x] + wbase;   // first row of this warp
   if (vis) {
     ObsLin o;
-    obs_linearize<true>(cam, x[3 * p], x[3 * p + 1], x[3 * p + 2], yy.x, yy.y, sc, o);
+    obs_linearize<true, true>(cam, x[3 * p], x[3 * p + 1], x[3 * p + 2], yy.x, yy.y, sc, o);
     r2[row0 + wr] = make_double2(o.e0, o.e1);
     if (obs_cam) { obs_cam[row0 + wr] = c; obs_pt[row0 + wr] = (int32_t)p; }
     double2* st = &stage[warp][wr * 9];

@@ -37,11 +37,11 @@ k_build_yhat(const double* __restrict__ campack, const double* __restrict__ x, c
   double V[6];
 #pragma unroll
   for (int k = 0; k < 6; ++k) V[k] = Vp[6 * p + k];
-  const Chol3 L = chol3(V, alpha);
+  const Chol3r L = chol3r(V, alpha);
   double* col = Yhat + 3 * p;
   {  // bt = L^-1 (-g_p)
     double a = -gp[3 * p], b = -gp[3 * p + 1], d = -gp[3 * p + 2];
-    chol3_fwd(L, a, b, d);
+    chol3r_fwd(L, a, b, d);
     double* o = col + (size_t)(6 * C + B) * ldy;
     o[0] = a; o[1] = b; o[2] = d;
   }
@@ -53,7 +53,7 @@ k_build_yhat(const double* __restrict__ campack, const double* __restrict__ x, c
       if (b >= 0) {
         double u[3];
         bone_u_dev(x, fb, bones, b, joint_bones[(j * BAX_MAX_JB + k) * 2 + 1], Lbar, scale, u);
-        chol3_fwd(L, u[0], u[1], u[2]);
+        chol3r_fwd(L, u[0], u[1], u[2]);
         double* o = col + (size_t)(6 * C + b) * ldy;
         o[0] = u[0]; o[1] = u[1]; o[2] = u[2];
       }
@@ -87,7 +87,7 @@ k_build_yhat(const double* __restrict__ campack, const double* __restrict__ x, c
       double w0 = j0 * o.jp[0][0] + j1 * o.jp[1][0];
       double w1 = j0 * o.jp[0][1] + j1 * o.jp[1][1];
       double w2 = j0 * o.jp[0][2] + j1 * o.jp[1][2];
-      chol3_fwd(L, w0, w1, w2);                  // row i of Y_p = (L^-1 W_i^T)^T
+      chol3r_fwd(L, w0, w1, w2);                  // row i of Y_p = (L^-1 W_i^T)^T
       double* q = col + (size_t)(6 * c + i) * ldy;
       q[0] = w0; q[1] = w1; q[2] = w2;
     }
@@ -135,12 +135,12 @@ k_backsub(const double* __restrict__ s, int64_t P, int C, int J, int B, const in
     double V[6];
 #pragma unroll
     for (int k = 0; k < 6; ++k) V[k] = Vp[6 * p + k];
-    const Chol3 L = chol3(V, alpha);
-    chol3_bwd(L, a0, a1, a2);                    // p_p
+    const Chol3r L = chol3r(V, alpha);
+    chol3r_bwd(L, a0, a1, a2);                    // p_p
     step_pts[3 * p] = a0; step_pts[3 * p + 1] = a1; step_pts[3 * p + 2] = a2;
     acc[0] = a0 * a0 + a1 * a1 + a2 * a2;
     acc[1] = gp[3 * p] * a0 + gp[3 * p + 1] * a1 + gp[3 * p + 2] * a2;
-    chol3_fwd(L, a0, a1, a2);                    // L^-1 p_p
+    chol3r_fwd(L, a0, a1, a2);                    // L^-1 p_p
     bt[0] = a0; bt[1] = a1; bt[2] = a2;
     acc[2] = a0 * a0 + a1 * a1 + a2 * a2;
   }
