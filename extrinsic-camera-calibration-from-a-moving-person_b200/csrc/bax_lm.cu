@@ -523,6 +523,7 @@ extern "C" int bax_linearize_finish(bax_handle* h, double* out_host, void* strea
   k_lin_stage<<<1, 256, 0, s>>>(lin + (size_t)C6 * C6, h->buf[BAX_BUF_NORM], h->buf[BAX_BUF_GMAX], h->buf[BAX_BUF_BONE] + B,
                                 h->theta_lin, C6, B, h->lin_stage);
   BAX_LAUNCH_CHECK();
+  h->t_launch[BAX_T_LIN] += 1;
   double* stage = h->host_pinned + 64;
   BAX_CUDA(cudaMemcpyAsync(stage, h->lin_stage, sizeof(double) * n_stage, cudaMemcpyDeviceToHost, s));
   BAX_CUDA(cudaStreamSynchronize(s));

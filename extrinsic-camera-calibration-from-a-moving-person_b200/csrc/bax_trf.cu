@@ -138,6 +138,7 @@ extern "C" int bax_trf_iterate(bax_handle* h, bax_trf_state* st, void* stream) {
     const double predicted = -(0.5 * kappa * kappa * (-tr.gdotp - alpha * p_norm * p_norm) + kappa * tr.gdotp);
     k_axpy_out<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(n, st->x, st->step, kappa, st->x_new);
     BAX_LAUNCH_CHECK();
+    h->t_launch[BAX_T_LIN] += 1;
     if ((rc = bax_linearize_push(h))) return rc;
     if ((rc = linearize(h, st->x_new, ln, s))) return rc;
     st->nfev += 1;

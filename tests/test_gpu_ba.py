@@ -443,3 +443,40 @@ def test_native_trust_region_driver_same_path(golden_dir, case):
     res = sol.result()
     assert res["status"] == (0 if s1 is None else s1) and res["njev"] == nj1
     prob.close()
+
+
+@pytest.mark.parametrize("C,N,lam1,lam2,drop3d", [(2, 6, 1.0, 10.0, 0.0),      # the smallest rig the objective accepts
+                                                  (4, 1, 1.0, 10.0, 0.0),      # one frame: bone-length variance is 0
+                                                  (3, 9, 0.0, 0.0, 0.1),       # both priors switched off
+                                                  (5, 7, 3.0, 0.0, 1.0),       # no 3-D pose valid anywhere: no orientation rows
+                                                  (3, 40, 1.0, 1e5, 0.05)])    # GAFA-like lambda2 (run_gafa.sh:3)
+def test_edge_shapes_vs_oracle(C, N, lam1, lam2, drop3d):
+    """Ragged / degenerate shapes: residual vector, cost, gradient and one damped step against the oracle."""
+    sc = scene.make_scene(C=C, N=N, seed=900 + C + N, score_mode="uniform", p_drop_2d=0.2 if C > 2 else 0.0,
+                          p_drop_3d=min(drop3d, 0.99))
+    sp2d, ss2d, sp3d, ss3d = scene.ba_inputs(sc)
+    if drop3d >= 1.0:
+        ss3d = np.zeros_like(ss3d)
+    J = ss2d.shape[2]
+    prob = ba.BAProblem(sc.K, sp2d, ss2d, sp3d, ss3d, ba.OP_BONE, lam1, lam2)
+    x0 = prob.triangulate(sc.R_init, sc.t_init)
+    th = ba.to_theta(sc.R_init, sc.t_init, x0.reshape(-1, 3))
+    assert np.all(np.isfinite(th))
+    args = (sc.K, sp2d.reshape(C, N * J, 2), ss2d, sp3d, ss3d, bo.OP_BONE, C, N, J, lam1, lam2)
+    f = bo.objfun(th, *args)
+    r = prob.residual(th).cpu().numpy()
+    assert r.shape == f.shape and _rel(r, f) <= 1e-9
+    if drop3d >= 1.0:
+        assert prob.n_v3d == 0
+    Jd = bo.jacobian(th, *args).toarray()
+    cost, ginf, g2, xn = prob.linearize(th)
+    grad = Jd.T @ f
+    assert abs(cost - 0.5 * f @ f) <= 1e-10 * max(cost, 1e-300)
+    assert abs(g2 - np.linalg.norm(grad)) <= 1e-8 * g2 and abs(ginf - np.max(np.abs(grad))) <= 1e-8 * ginf
+    alpha = 0.01 * g2 / xn
+    prob.trial(alpha, True)
+    p_ref = np.linalg.solve(Jd.T @ Jd + alpha * np.eye(Jd.shape[1]), -grad)
+    assert np.linalg.norm(prob.step.cpu().numpy() - p_ref) <= 1e-7 * np.linalg.norm(p_ref)
+    R, t, x = ba.ba_main(sc.camid, sc.K, sc.R_init, sc.t_init, sp2d, ss2d, sp3d, ss3d, lam1, lam2, verbose=False)
+    assert np.all(np.isfinite(R)) and np.all(np.isfinite(t)) and x.shape == (N * J, 3)
+    prob.close()
