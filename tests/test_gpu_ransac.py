@@ -120,3 +120,29 @@ def test_cfg2_scale_properties():
     Rgt = sc.R_gt[1] @ sc.R_gt[0].T
     assert np.max(np.abs(R[1] - Rgt)) < 0.05
     prob.close()
+
+
+def test_cfg2_pipeline_ransac_then_ba_refinement():
+    """BASELINE configs[1] end to end on the cfg1 scene (4 cameras x 1000 frames, sigma = 3 px): RANSAC linear
+    calibration (20 000 of the 100 000 hypotheses, to keep the suite short), then ba.py's refinement started from its
+    output, then the reference's own evaluation (eval.py: similarity alignment to the ground truth).  Sanity, not
+    parity: the refinement lowers the reprojection error and lands near the ground-truth rig."""
+    from calib_b200 import ba, eval as ev
+    sc = scene.cfg1(seed=2000)
+    v, n = cr.ransac_inputs(sc.p3d, sc.s3d, sc.p2d, sc.s2d, sc.K, OP_BONE)
+    R0, t0, _ = cr.calib_linear_ransac(v, n, sc.K, 20000, 50.0, 5.0 / 180 * np.pi, 0, verbose=False)
+    assert R0.shape == (4, 3, 3) and t0.shape == (4, 3, 1) and np.all(np.isfinite(R0)) and np.all(np.isfinite(t0))
+    sp2d, ss2d, sp3d, ss3d = scene.ba_inputs(sc)
+    R1, t1, x1, info = ba.ba_main(sc.camid, sc.K, R0, t0, sp2d, ss2d, sp3d, ss3d, 1.0, 1.0, verbose=False, return_info=True)
+    assert info["status"] in (1, 2, 3, 4) and info["cost"] < info["initial_cost"]
+    gt = sc.t_gt.reshape(-1, 3, 1)
+    J = ss2d.shape[2]
+    Xw = np.array(sc.X_w)[:, :J]
+
+    def errors(R, t):
+        return ev.eval_metrics(sc.K, R, t, sc.R_gt, gt, sp2d, ss2d, Xw, 1, 1.0)
+    R0o = np.array([ba.rodrigues(ba.rodrigues_inv(r)) for r in R0])          # what to_theta makes of the linear rotations
+    ER0, Et0, Ep0, Ex0 = errors(R0o, t0)
+    ER1, Et1, Ep1, Ex1 = errors(R1, t1)
+    assert np.mean(Ep1) < np.mean(Ep0) and np.mean(Ep1) < 6.0               # pixels; the noise alone is 3 px per axis
+    assert np.max(ER1) < 0.03 and np.max(ER1) <= np.max(ER0) + 1e-3        # rad / sqrt(2)
