@@ -57,6 +57,7 @@ _SIGS = {
     "bax_trial_begin": (i32, [vp, f64, vp]),
     "bax_trial_mid": (i32, [vp, vp, i32, vp]),
     "bax_trial_finish": (i32, [vp, P_f64, vp]),
+    "bax_trial_phi_prime": (i32, [vp, vp]),
     "bax_trf_begin": (i32, [vp, C.POINTER(TrfState), vp]),
     "bax_trf_iterate": (i32, [vp, C.POINTER(TrfState), vp]),
     "bax_trf_solve": (i32, [vp, C.POINTER(TrfState), vp]),
@@ -67,7 +68,7 @@ _SIGS = {
     "bax_timing_reset": (i32, [vp]),
 }
 
-BUF_BONE, BUF_COST, BUF_LIN, BUF_SCHUR, BUF_RHS2, BUF_STEP, BUF_NORM, BUF_GMAX = range(8)
+BUF_BONE, BUF_COST, BUF_LIN, BUF_SCHUR, BUF_RHS2, BUF_STEP, BUF_NORM, BUF_GMAX, BUF_RHS2_HEAD = range(9)
 T_NAMES = ["rj", "build", "syrk", "dense", "backsub", "linearize", "cost", "other"]
 
 

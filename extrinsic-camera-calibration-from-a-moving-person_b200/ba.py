@@ -328,6 +328,16 @@ class BAProblem:
             raise BaxError(f"non-finite trial step at alpha={alpha}: reduced camera system not SPD")
         return pn2, gp, ptq
 
+    def trial_phi_prime(self):
+        """p^T (J^T J + alpha I)^-1 p of the last trial(alpha, False), computed on demand (second right-hand side from
+        the whitened blocks still on the device + second reduced solve)."""
+        st = _stream()
+        with torch.cuda.device(self.dev):
+            check(self.L.bax_trial_phi_prime(self.h, st), "bax_trial_phi_prime")
+            self._allreduce(_lib.BUF_RHS2_HEAD)
+            check(self.L.bax_trial_finish(self.h, self._out4, st), "bax_trial_finish")
+        return self._out4[2]
+
     def triangulate(self, R_w2c, t_w2c):
         """util.triangulate_with_conf (reference util.py:325-354) -> (N,J,3) numpy."""
         f = dict(dtype=torch.float64, device=self.dev)
@@ -398,11 +408,16 @@ def _solve_tr(prob, Delta, g_norm2, initial_alpha, rtol=0.01, max_iter=10):
         if alpha < alpha_lower or alpha > alpha_upper:
             alpha = reset()
         alpha = max(alpha, alpha_floor)
-        pn2, gp, ptq = prob.trial(alpha, True)
+        # phi' costs another pass over the whitened blocks and a second reduced solve: at the floor the step is usually
+        # the interior one and returns before phi' is looked at, so it is computed only once that is ruled out
+        lazy = alpha <= alpha_floor
+        pn2, gp, ptq = prob.trial(alpha, not lazy)
         p_norm = math.sqrt(pn2)
         phi = p_norm - Delta
         if phi < 0 and alpha <= alpha_floor:
             return alpha, it + 1, p_norm, gp, False          # interior (Gauss-Newton-like) step
+        if lazy:
+            ptq = prob.trial_phi_prime()
         if not (ptq > 0 and p_norm > 0):
             break                                             # step underflowed (start is already stationary)
         phi_prime = -ptq / p_norm

@@ -354,7 +354,8 @@ extern "C" int bax_problem_dims(bax_handle* h, int64_t* d) {
 }
 
 extern "C" int bax_reduce_buffer(bax_handle* h, int which, double** p, int64_t* n) {
-  if (!h || which < 0 || which >= 8 || !h->campack) { bax_set_error("bax_reduce_buffer: bad argument"); return BAX_E_ARG; }
+  if (!h || which < 0 || which > BAX_BUF_RHS2_HEAD || !h->campack) { bax_set_error("bax_reduce_buffer: bad argument"); return BAX_E_ARG; }
+  if (which == BAX_BUF_RHS2_HEAD) { *p = h->buf[BAX_BUF_RHS2]; *n = 6 * h->C + h->B; return BAX_OK; }   // without the already-summed tail
   *p = h->buf[which]; *n = h->buf_count[which];
   return BAX_OK;
 }

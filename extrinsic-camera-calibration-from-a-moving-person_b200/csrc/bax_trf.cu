@@ -63,9 +63,16 @@ int solve_tr(bax_handle* h, bax_trf_state* st, double Delta, double g_norm2, dou
   for (it = 0; it < max_iter; ++it) {
     if (alpha < alpha_lower || alpha > alpha_upper) alpha = reset();
     alpha = fmax(alpha, alpha_floor);
-    if ((rc = trial(h, st, alpha, 1, o, s))) return rc;
+    // phi' costs another pass over the whitened blocks and a second reduced solve: at the floor the step is usually
+    // the interior one and returns before phi' is looked at, so it is computed only once that is ruled out
+    const bool lazy = alpha <= alpha_floor;
+    if ((rc = trial(h, st, alpha, lazy ? 0 : 1, o, s))) return rc;
     const double p_norm = sqrt(o[0]), phi = p_norm - Delta;
     if (phi < 0 && alpha <= alpha_floor) { r = {alpha, it + 1, p_norm, o[1], false}; return BAX_OK; }
+    if (lazy) {
+      if ((rc = bax_trial_phi_prime(h, s))) return rc;
+      if ((rc = bax_trial_finish(h, o, s))) return rc;
+    }
     if (!(o[2] > 0 && p_norm > 0)) break;
     const double phi_prime = -o[2] / p_norm;
     if (phi < 0) alpha_upper = alpha;

@@ -164,6 +164,18 @@ k_gemv_last(const double* __restrict__ Yhat, int64_t ldy, int64_t K, int last, i
   if (threadIdx.x == 0) part[(size_t)blockIdx.y * rows + i] = acc[0];
 }
 
+// rhs2[0 .. 6C+B) = Yhat[0 .. 6C+B) . (L^-1 p)   (the row k_backsub left in place of bt)
+static int launch_phi_rhs(bax_handle* h, cudaStream_t s) {
+  const int C6 = 6 * h->C, B = h->B;
+  int64_t K = 3 * h->P, chunk = 1 << 15;
+  int nch = (int)((K + chunk - 1) / chunk);
+  double* part2 = h->partials + (size_t)(1 << 21);
+  if ((size_t)nch * (C6 + B) > (1u << 21)) { bax_set_error("partials overflow in gemv"); return BAX_E_STATE; }
+  k_gemv_last<<<dim3(C6 + B, nch), 256, 0, s>>>(h->Yhat, h->ldy, K, C6 + B, chunk, C6 + B, part2);
+  BAX_LAUNCH_CHECK();
+  return bax_reduce_partials(h, part2, nch, C6 + B, h->buf[BAX_BUF_RHS2], s);
+}
+
 extern "C" int bax_trial_begin(bax_handle* h, double alpha, void* stream) {
   if (!h || !h->Yhat || !(alpha > 0)) { bax_set_error("bax_trial_begin: needs a linearised problem and alpha > 0"); return BAX_E_ARG; }
   cudaStream_t s = (cudaStream_t)stream;
@@ -201,19 +213,29 @@ extern "C" int bax_trial_mid(bax_handle* h, double* step, int need_phi_prime, vo
     double* rhs2 = h->buf[BAX_BUF_RHS2];
     rc = bax_reduce_partials(h, part, nb, 3, rhs2 + C6 + B, s); if (rc) return rc;
     if (need_phi_prime) {
-      int64_t K = 3 * h->P, chunk = 1 << 15;
-      int nch = (int)((K + chunk - 1) / chunk);
-      double* part2 = h->partials + (size_t)(1 << 21);
-      if ((size_t)nch * (C6 + B) > (1u << 21)) { bax_set_error("partials overflow in gemv"); return BAX_E_STATE; }
-      k_gemv_last<<<dim3(C6 + B, nch), 256, 0, s>>>(h->Yhat, h->ldy, K, C6 + B, chunk, C6 + B, part2);
-      BAX_LAUNCH_CHECK();
-      rc = bax_reduce_partials(h, part2, nch, C6 + B, rhs2, s); if (rc) return rc;
+      rc = launch_phi_rhs(h, s); if (rc) return rc;
     } else {
       BAX_CUDA(cudaMemsetAsync(rhs2, 0, sizeof(double) * (C6 + B), s));
     }
   }
   h->t_launch[BAX_T_BACKSUB] += need_phi_prime ? 2 : 0;
   h->need_phi = need_phi_prime;
+  return BAX_OK;
+}
+
+// phi'(alpha) on demand: after a bax_trial_mid(.., need_phi_prime = 0, ..) / bax_trial_finish pair whose step turned
+// out NOT to be the interior one, the right-hand side of the second reduced solve is formed now (the whitened blocks
+// and L^-1 p are still in Yhat); the caller all-reduces BAX_BUF_RHS2_HEAD (frame-sharded runs) and calls
+// bax_trial_finish again.  The interior (Gauss-Newton-like) steps — most steps of a converging run — never pay for it.
+extern "C" int bax_trial_phi_prime(bax_handle* h, void* stream) {
+  if (!h || !h->Yhat) { bax_set_error("bax_trial_phi_prime: no damped solve to extend"); return BAX_E_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  BAX_CUDA(cudaSetDevice(h->device));
+  {
+    BaxTimer t(h, BAX_T_BACKSUB, s, 2);
+    int rc = launch_phi_rhs(h, s); if (rc) return rc;
+  }
+  h->need_phi = 1;
   return BAX_OK;
 }
 

@@ -72,7 +72,8 @@ int bax_prior_jacobian(bax_handle* h, const double* theta, double* Jv3d, double*
  * so the host can all-reduce it in place (NCCL via torch.distributed) between the two calls.
  * On one GPU the *_finish call simply follows. */
 enum { BAX_BUF_BONE = 0, BAX_BUF_COST = 1, BAX_BUF_LIN = 2, BAX_BUF_SCHUR = 3, BAX_BUF_RHS2 = 4,
-       BAX_BUF_STEP = 5 /* not reduced: trial scalars */, BAX_BUF_NORM = 6, BAX_BUF_GMAX = 7 /* MAX-reduced */ };
+       BAX_BUF_STEP = 5 /* not reduced: trial scalars */, BAX_BUF_NORM = 6, BAX_BUF_GMAX = 7 /* MAX-reduced */,
+       BAX_BUF_RHS2_HEAD = 8 /* the first 6C+B doubles of BAX_BUF_RHS2: what bax_trial_phi_prime fills */ };
 int bax_reduce_buffer(bax_handle* h, int which, double** dev_ptr, int64_t* count);
 /* global frame count used by the bone-length variance (sum of N over ranks); default = local N */
 int bax_set_global_frames(bax_handle* h, int64_t n_frames_global);
@@ -104,6 +105,9 @@ int bax_linearize_pop(bax_handle* h);
 int bax_trial_begin(bax_handle* h, double alpha, void* stream);
 int bax_trial_mid(bax_handle* h, double* step, int need_phi_prime, void* stream);
 int bax_trial_finish(bax_handle* h, double* out_host, void* stream);
+/* phi'(alpha) on demand, after a mid(need_phi_prime = 0) / finish pair: forms the second right-hand side
+ * (-> BAX_BUF_RHS2_HEAD, to be all-reduced by a frame-sharded run); call bax_trial_finish again for out_host[2]. */
+int bax_trial_phi_prime(bax_handle* h, void* stream);
 
 /* ---- whole trust-region iterations behind one call (one GPU; a frame-sharded run all-reduces between the phases
  * above and is driven from the host language instead).  Same scalar logic as SciPy's trf_no_bounds
