@@ -408,6 +408,9 @@ def run_gpu(args):
     # ---------------- RANSAC leg (hypotheses/s), BASELINE configs[1]
     from calib_b200 import calib_ransac as cr
     rs = cr.bench_leg(rank, world, dev, steps=max(1, min(args.steps, 3)), no_cpu=args.no_cpu or world > 1)
+    cpu_in = rs.pop("_cpu_inputs", None)
+    if cpu_in is not None:
+        rs["cpu_baseline"] = ransac_cpu_leg(**cpu_in)
     if line is not None:
         line["ransac"] = rs
         line["gpu_launches"] = int(launches) + sum(v["launches"] for v in rs["kernel_ms_one_pass"].values()) * max(1, min(args.steps, 3))
@@ -420,6 +423,23 @@ def run_gpu(args):
     prob.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def ransac_cpu_leg(v, n, sn, sm, scores, budget_s=15.0):
+    """cpu_baseline of the RANSAC leg: the first hypotheses of the same sample stream through the oracle port on one
+    host core (bounded to ~15 s), their scores compared with the GPU's."""
+    from oracle import ransac_oracle as ro
+    k, t2, worst = 0, time.perf_counter(), 0.0
+    while k < len(sn) and (time.perf_counter() - t2 < budget_s or k < 2):
+        Rh, th_, _ = ro.calib_linear(v[:, sn[k]], n[:, sm[k]])
+        _, _, es, e3s = ro.score_hypothesis(Rh, th_, v, n)
+        worst = max(worst, abs(es + e3s - scores[k]) / (es + e3s))
+        k += 1
+    dt = time.perf_counter() - t2
+    return {"value": k / dt, "unit": "hypotheses/s", "cores": 1, "kind": "port",
+            "sample": f"first {k} hypotheses of the same seed at full M, N_o through the vectorised oracle port "
+                      f"(the literal reference loop is ~20x slower, SURVEY.md §6)",
+            "max_rel_score_diff_vs_gpu": worst}
 
 
 def batch_leg(rank, world, group, n_per_gpu=64, n_streams=12):
@@ -481,19 +501,73 @@ def run_local_single(mine, ba):
     return time.perf_counter() - t0, out
 
 
+def run_cpu_rows(args):
+    """`--impl cpu_rows`: the CPU rows that stand beside the GPU numbers, on this box's host
+    cores.  literal: SciPy least_squares(trf, dense 2-point finite differences, dense SVD) on the oracle port of ba.objfun —
+    what reference ba.py:187-206 runs — at frame counts small enough to execute.  strong: NOT the reference: the same
+    objective with the oracle's analytic sparse Jacobian through least_squares(jac=..., tr_solver='lsmr') at the cfg1 size."""
+    from scipy.optimize import least_squares
+    import calib_b200  # noqa: F401
+    from calib_b200 import scene
+    from oracle import ba_oracle as bo
+    out = {"host_cpus": os.cpu_count(), "literal": [], "strong": None}
+    budget = float(os.environ.get("CPU_ROWS_BUDGET_S", "60"))
+    t_start = time.perf_counter()
+    for N in (5, 10, 20, 40):
+        if time.perf_counter() - t_start > budget:
+            break
+        sc = scene.cfg1(seed=300 + N, N=N)
+        sp2d, ss2d, sp3d, ss3d = scene.ba_inputs(sc)
+        C, _, J = ss2d.shape
+        x0 = bo.triangulate_with_conf(sp2d, ss2d, sc.K, sc.R_init, sc.t_init.reshape(C, 3, 1), ss2d > 0)
+        th0 = bo.to_theta(sc.R_init, sc.t_init, x0.reshape(-1, 3))
+        args = (sc.K, sp2d.reshape(C, N * J, 2), ss2d, sp3d, ss3d, bo.OP_BONE, C, N, J, 1.0, 1.0)
+        t0 = time.perf_counter()
+        res = least_squares(bo.objfun, th0, method="trf", ftol=1e-4, args=args)
+        dt = time.perf_counter() - t0
+        n_obs = int((ss2d > 0).sum())
+        out["literal"].append({"frames": N, "n": int(th0.size), "m": int(res.fun.size), "observations": n_obs,
+                               "seconds": dt, "iterations": int(res.njev), "nfev": int(res.nfev),
+                               "s_per_iteration": dt / res.njev, "obs_per_s_per_iteration": n_obs * res.njev / dt,
+                               "status": int(res.status)})
+    # strong CPU row at cfg1
+    sc = scene.cfg1(seed=0, N=int(os.environ.get("CPU_ROWS_STRONG_N", "1000")))
+    sp2d, ss2d, sp3d, ss3d = scene.ba_inputs(sc)
+    C, N, J = ss2d.shape
+    t0 = time.perf_counter()
+    x0 = bo.triangulate_with_conf(sp2d, ss2d, sc.K, sc.R_init, sc.t_init.reshape(C, 3, 1), ss2d > 0)
+    t_tri = time.perf_counter() - t0
+    th0 = bo.to_theta(sc.R_init, sc.t_init, x0.reshape(-1, 3))
+    args = (sc.K, sp2d.reshape(C, N * J, 2), ss2d, sp3d, ss3d, bo.OP_BONE, C, N, J, 1.0, 1.0)
+    t0 = time.perf_counter()
+    res = least_squares(bo.objfun, th0, jac=bo.jacobian, method="trf", tr_solver="lsmr", ftol=1e-4, args=args,
+                        max_nfev=int(os.environ.get("CPU_ROWS_STRONG_NFEV", "12")))
+    dt = time.perf_counter() - t0
+    n_obs = int((ss2d > 0).sum())
+    out["strong"] = {"frames": N, "n": int(th0.size), "observations": n_obs, "seconds": dt, "iterations": int(res.njev),
+                     "nfev": int(res.nfev), "s_per_iteration": dt / res.njev,
+                     "obs_per_s_per_iteration": n_obs * res.njev / dt, "status": int(res.status),
+                     "triangulation_s": t_tri,
+                     "note": "analytic sparse Jacobian + LSMR trust-region solver; not what the reference runs"}
+    print(json.dumps(out))
+
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=60)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default="cfg4shard", choices=sorted(WORKLOADS))
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "cpu_rows"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--batch", type=int, default=64, help="problems per GPU of the sweep leg (0 = skip)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3
-    if args.impl == "reference":
+    if args.impl == "cpu_rows":
+        run_cpu_rows(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_gpu(args)
