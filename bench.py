@@ -25,6 +25,10 @@ WORKLOADS = {
     # shard is 12 500 frames, so N GPUs hold N x 12 500 frames (weak scaling; N = 8 is the full config).
     "cfg4shard": dict(C=64, N=12500, kind="cfg4", lam=(1.0, 1.0),
                       name="cfg4 shard: 64 cameras x 12500 frames/GPU x 17 joints (8 GPUs = BASELINE configs[3], 1.088e8 obs)"),
+    # the whole of configs[3] on ONE GPU (it fits: observations 2.6 GB, whitened blocks 16 GB); not the default because
+    # the N-GPU runs are weak-scaling over shards and 8 shards make exactly this scene
+    "cfg4full": dict(C=64, N=100000, kind="cfg4", lam=(1.0, 1.0),
+                     name="cfg4 full: 64 cameras x 100000 frames x 17 joints on one GPU (BASELINE configs[3], 1.088e8 obs)"),
     "cfg3": dict(C=31, N=10000, kind="cfg3", lam=(100.0, 1.0),
                  name="cfg3: Panoptic-shaped, 31 cameras x 10000 frames x 17 joints, 30% dropped detections (per GPU)"),
     "cfg1": dict(C=4, N=1000, kind="cfg1", lam=(1.0, 1.0),
