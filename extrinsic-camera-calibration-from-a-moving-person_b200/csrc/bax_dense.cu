@@ -274,6 +274,34 @@ __device__ void chol32_cta(double* Dg, double* rinv, double* colbuf /*[2][32]*/)
   for (int q = 0; q < 4; ++q) Dg[r * LDS_ + cg + 8 * q] = e[q];
   __syncthreads();
 }
+// The same factorisation by ONE warp out of registers: lane r keeps row r (32 doubles), the pivot and the column
+// entries travel by shuffle, no barrier and no shared-memory round trip per column (the 256-thread version above spends
+// ~720 cycles per column on them: 23k cycles per block, a third of the cooperative solve at 384 unknowns).  Same
+// arithmetic per entry as chol32_cta (bitwise).  Ends with a CTA barrier.
+__device__ void chol32_warp(double* Dg, double* rinv) {
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    double e[NBK];
+#pragma unroll
+    for (int c = 0; c < NBK; ++c) e[c] = Dg[lane * LDS_ + c];
+#pragma unroll
+    for (int k = 0; k < NBK; ++k) {
+      const double piv = __shfl_sync(0xffffffffu, e[k], k);
+      const double ri = rsqrt(piv);
+      const double lr = e[k] * ri;                 // L[lane][k] (lanes < k: unused upper part)
+      e[k] = lr;
+      if (lane == k) rinv[k] = ri;
+#pragma unroll
+      for (int c = k + 1; c < NBK; ++c) {
+        const double lc = __shfl_sync(0xffffffffu, lr, c);       // L[c][k]
+        e[c] = fma(-lr, lc, e[c]);
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < NBK; ++c) Dg[lane * LDS_ + c] = e[c];
+  }
+  __syncthreads();
+}
 // X <- X L^-T for 32 rows held in Pn (row-major, stride LDS_), L = Dg with reciprocal diagonal rinv
 __device__ void trsm32_cta(double* Pn, const double* Dg, const double* rinv) {
   const int tid = threadIdx.x, r = tid >> 3, cg = tid & 7, lane = tid & 31;
@@ -296,7 +324,7 @@ __device__ void trsm32_cta(double* Pn, const double* Dg, const double* rinv) {
 
 __global__ void __launch_bounds__(CG_THREADS)
 k_dense_solve1_coop(const double* __restrict__ schur, int R, const double* __restrict__ lin, int n, int B, double alpha,
-                    double* __restrict__ ws, double* __restrict__ coef, int prof) {
+                    double* __restrict__ ws, double* __restrict__ coef, int prof, int chol_warp) {
   long long tp[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; long long tc = clock64();
 #define PROF(i) { long long t_ = clock64(); tp[i] += t_ - tc; tc = t_; }
   cg::grid_group grid = cg::this_grid();
@@ -370,7 +398,7 @@ k_dense_solve1_coop(const double* __restrict__ schur, int R, const double* __res
     }
     __syncthreads();
     PROF(3)
-    chol32_cta(Dg, rinv, colbuf);             // ends with a CTA barrier
+    if (chol_warp) chol32_warp(Dg, rinv); else chol32_cta(Dg, rinv, colbuf);   // both end with a CTA barrier
     PROF(4)
     if (cta == 0)
       for (int idx = tid; idx < nb * nb; idx += nt) {
@@ -557,7 +585,9 @@ int bax_dense_solve1(bax_handle* h, cudaStream_t s) {
     const double* schur = h->buf[BAX_BUF_SCHUR]; const double* lin = h->buf[BAX_BUF_LIN];
     int R = h->R, nn = n, B = h->B; double alpha = h->alpha; double* ws = h->dense_ws; double* coef = h->coef;
     int prof = h->dense_coop > 1;
-    void* args[] = {(void*)&schur, (void*)&R, (void*)&lin, (void*)&nn, (void*)&B, (void*)&alpha, (void*)&ws, (void*)&coef, (void*)&prof};
+    static const int chol_warp = getenv("BAX_CHOL_WARP") ? atoi(getenv("BAX_CHOL_WARP")) : 1;   // 0: the 256-thread diagonal-block factorisation
+    int cw = chol_warp;
+    void* args[] = {(void*)&schur, (void*)&R, (void*)&lin, (void*)&nn, (void*)&B, (void*)&alpha, (void*)&ws, (void*)&coef, (void*)&prof, (void*)&cw};
     BaxTimer t(h, BAX_T_DENSE, s, 1);
     BAX_CUDA(cudaLaunchCooperativeKernel((void*)k_dense_solve1_coop, dim3(G), dim3(CG_THREADS), args, sm, s));
     return BAX_OK;
