@@ -9,30 +9,18 @@ namespace cg = cooperative_groups;
 
 // In-place lower Cholesky of A (n x n, row-major, leading dimension ld, global/L2 resident).
 // Dg: [32][33] shared, Pn: [(n-32)][33] shared.  Right-looking, 32-wide panels, 4x4 register tiles.
+__device__ void chol32_warp(double* Dg, double* rinv);
 __device__ void chol_blocked(double* __restrict__ A, int n, int ld, double* Dg, double* Pn) {
-  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ double rinv_s[NBK];
+  const int tid = threadIdx.x, nt = blockDim.x;
   for (int j0 = 0; j0 < n; j0 += NBK) {
     const int nb = min(NBK, n - j0);
-    for (int idx = tid; idx < nb * nb; idx += nt) {
-      int r = idx / nb, c = idx % nb;
-      Dg[r * LDS_ + c] = A[(size_t)(j0 + r) * ld + j0 + c];
+    for (int idx = tid; idx < NBK * NBK; idx += nt) {      // lower part; identity beyond nb (chol32_warp works on 32 x 32)
+      const int r = idx >> 5, c = idx & 31;
+      Dg[r * LDS_ + c] = (r < nb && c <= r) ? A[(size_t)(j0 + r) * ld + j0 + c] : (r == c ? 1.0 : 0.0);
     }
     __syncthreads();
-    if (warp == 0) {
-      for (int k = 0; k < nb; ++k) {
-        double dkk = sqrt(Dg[k * LDS_ + k]);
-        __syncwarp();
-        if (lane == k) Dg[k * LDS_ + k] = dkk;
-        if (lane > k && lane < nb) Dg[lane * LDS_ + k] /= dkk;
-        __syncwarp();
-        if (lane > k && lane < nb) {
-          double lk = Dg[lane * LDS_ + k];
-          for (int c = k + 1; c <= lane; ++c) Dg[lane * LDS_ + c] -= lk * Dg[c * LDS_ + k];
-        }
-        __syncwarp();
-      }
-    }
-    __syncthreads();
+    chol32_warp(Dg, rinv_s);                               // ends with a CTA barrier
     for (int idx = tid; idx < nb * nb; idx += nt) {
       int r = idx / nb, c = idx % nb;
       if (c <= r) A[(size_t)(j0 + r) * ld + j0 + c] = Dg[r * LDS_ + c];
