@@ -585,6 +585,11 @@ class TRFSolver:
                                              self.ftol, self.xtol)
             if self.status is not None:
                 break
+            if not on_boundary:
+                # SciPy returns alpha = 0 for an interior Gauss-Newton step (common.py:113-116) and starts the next
+                # sub-problem from there; carrying the floor value instead costs a wasted damped solve whenever the
+                # Hessian scale (hence the floor) drops a little between linearisations
+                self.alpha = 0.0
             self.alpha *= self.Delta / Delta_new
             self.Delta = Delta_new
         if actual_reduction > 0:

@@ -167,6 +167,7 @@ extern "C" int bax_trf_iterate(bax_handle* h, bax_trf_state* st, void* stream) {
     }
     st->status = check_termination(actual, st->cost, step_norm, st->x_norm, ratio, st->ftol, st->xtol);
     if (st->status >= 0) break;
+    if (!tr.on_boundary) st->alpha = 0.0;        // SciPy's alpha after an interior step (see ba.py TRFSolver.iterate)
     st->alpha *= st->Delta / Delta_new;
     st->Delta = Delta_new;
   }

@@ -387,7 +387,7 @@ def trf_exact(fun, jac, x0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, floo
                 step, alpha, n_it = solve_lsq_trust_region(n, m, uf, s, V, Delta, initial_alpha=alpha)
             else:
                 floor = 1e-13 * np.max(np.sum(J[:, floor_cols:] ** 2, axis=0))
-                step, alpha, n_it, _ = solve_tr_floored(uf, s, V, Delta, alpha, floor)
+                step, alpha, n_it, on_b = solve_tr_floored(uf, s, V, Delta, alpha, floor)
             Js = J @ step
             predicted_reduction = -(0.5 * Js @ Js + g @ step)
             x_new = x + step
@@ -407,6 +407,8 @@ def trf_exact(fun, jac, x0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, floo
                                        ratio, ftol, xtol)
             if status is not None:
                 break
+            if floor_cols is not None and not on_b:
+                alpha = 0.0                      # what SciPy's solver returns for an interior step (common.py:113-116)
             alpha *= Delta / Delta_new
             Delta = Delta_new
         if actual_reduction > 0:
