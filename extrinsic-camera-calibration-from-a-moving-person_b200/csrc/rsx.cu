@@ -29,7 +29,8 @@ k_rsx_fit(int C, int64_t N, int64_t M, const double* __restrict__ v, const doubl
 __global__ void __launch_bounds__(32 * FITW_WARPS)
 k_rsx_fit_warp(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
                const int32_t* __restrict__ samp_v, const int32_t* __restrict__ samp_m, int64_t H,
-               double* __restrict__ Rt, unsigned long long* __restrict__ stats /*[3]: fall-backs, sweeps, work counter*/) {
+               double* __restrict__ Rt, unsigned long long* __restrict__ stats /*[4]: fall-backs, sweeps, work counter, deferred*/,
+               int32_t* __restrict__ deferred /*null: the warp runs the Jacobi fall-back itself*/) {
   extern __shared__ __align__(16) double sm[];
   const int nu = 3 * (RSX_S + C), ld = nu | 1;
   const size_t per_warp = (fit_ws_small_doubles(C) + 2 * (size_t)nu * ld + 1) & ~(size_t)1;
@@ -44,12 +45,33 @@ k_rsx_fit_warp(int C, int64_t N, int64_t M, const double* __restrict__ v, const 
     if (lane == 0) h = (long long)atomicAdd(stats + 2, 1ULL);
     h = __shfl_sync(0xffffffffu, h, 0);
     if (h >= H) break;
-    fit_hypothesis(g, C, N, M, v, n, samp_v + h * RSX_S, samp_m + h * RSX_S, ws, Rt + (size_t)h * C * 12, true);
-    if (stats && lane == 0) {
+    const bool done = fit_hypothesis(g, C, N, M, v, n, samp_v + h * RSX_S, samp_m + h * RSX_S, ws, Rt + (size_t)h * C * 12,
+                                     true, deferred != nullptr);
+    if (lane == 0) {
       const int sw = ws.iflag[8];
       if (sw < 0) atomicAdd(stats, 1ULL); else atomicAdd(stats + 1, (unsigned long long)sw);
+      if (!done) deferred[atomicAdd(stats + 3, 1ULL)] = (int32_t)h;     // second pass: k_rsx_fit_deferred
     }
     __syncwarp();
+  }
+}
+
+// Second pass over the hypotheses whose arrow iteration did not settle: one CTA each, the parallel cyclic Jacobi
+// diagonalisation.  A warp of k_rsx_fit_warp running it inline takes ~50 normal fits, and the few warps that met one
+// near the end of a chunk kept the whole GPU waiting (ncu: SMs active 62 % of the kernel's time).
+__global__ void __launch_bounds__(FIT_THREADS)
+k_rsx_fit_deferred(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
+                   const int32_t* __restrict__ samp_v, const int32_t* __restrict__ samp_m,
+                   const int32_t* __restrict__ deferred, const unsigned long long* __restrict__ stats,
+                   double* __restrict__ Rt) {
+  extern __shared__ __align__(16) double sm[];
+  FitWs ws;
+  fit_ws_carve(sm, nullptr, C, ws);
+  CtaCtx g{(int)threadIdx.x, (int)blockDim.x};
+  const unsigned long long nd = stats[3];
+  for (unsigned long long i = blockIdx.x; i < nd; i += gridDim.x) {
+    const int64_t h = deferred[i];
+    fit_hypothesis(g, C, N, M, v, n, samp_v + h * RSX_S, samp_m + h * RSX_S, ws, Rt + (size_t)h * C * 12, false);
   }
 }
 
@@ -182,7 +204,7 @@ extern "C" int rsx_destroy(rsx_handle* h) {
   cudaSetDevice(h->device);
   rsx_free_problem(h);
   if (h->bx) { if (h->bx->syrk_part) cudaFree(h->bx->syrk_part); if (h->bx->partials) cudaFree(h->bx->partials); free(h->bx); }
-  cudaFree(h->red); cudaFree(h->fit_stats); cudaFreeHost(h->host_pinned);
+  cudaFree(h->red); cudaFree(h->fit_stats); if (h->deferred) cudaFree(h->deferred); cudaFreeHost(h->host_pinned);
   cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
   free(h);
   return BAX_OK;
@@ -226,12 +248,28 @@ int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, 
       int64_t grid = (H + FITW_WARPS - 1) / FITW_WARPS;
       const int64_t cap = (int64_t)h->sm_count * per_sm;          // resident CTAs only: work is handed out dynamically
       if (grid > cap) grid = cap;
-      BAX_CUDA(cudaMemsetAsync((unsigned long long*)h->fit_stats + 2, 0, sizeof(unsigned long long), s));
+      BAX_CUDA(cudaMemsetAsync((unsigned long long*)h->fit_stats + 2, 0, 2 * sizeof(unsigned long long), s));
       BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_warp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      RsxTimer t(h, RSX_T_FIT, s, 1);
+      int32_t* deferred = nullptr;
+      if (h->fit_mode != 2 && small + hv <= 200 * 1024) {          // env RSX_FIT_MODE=2: fall-backs inline, as before
+        if (H > h->cap_deferred) {
+          if (h->deferred) cudaFree(h->deferred);
+          h->deferred = nullptr; h->cap_deferred = 0;
+          BAX_CUDA(cudaMalloc(&h->deferred, sizeof(int32_t) * H));
+          h->cap_deferred = H;
+        }
+        deferred = h->deferred;
+      }
+      RsxTimer t(h, RSX_T_FIT, s, deferred ? 2 : 1);
       k_rsx_fit_warp<<<(unsigned)grid, 32 * FITW_WARPS, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt,
-                                                                   (unsigned long long*)h->fit_stats);
+                                                                   (unsigned long long*)h->fit_stats, deferred);
       BAX_LAUNCH_CHECK();
+      if (deferred) {
+        BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_deferred, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(small + hv)));
+        k_rsx_fit_deferred<<<2 * h->sm_count, FIT_THREADS, small + hv, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, deferred,
+                                                                          (const unsigned long long*)h->fit_stats, Rt);
+        BAX_LAUNCH_CHECK();
+      }
       return BAX_OK;
     }
   }

@@ -34,10 +34,12 @@ __host__ __device__ inline void fit_ws_carve(double* base, double* HV /*null: ca
 
 // v: [C][N][3], n: [C][M][3] (global); sv, sm: the 10 + 10 sample indices; Rt_out: [C][12] rows [R_c | t_c].
 template <class G>
-__host__ __device__ inline void fit_hypothesis(const G& g, int C, int64_t N, int64_t M, const double* __restrict__ v,
+// defer = true: when the arrow iteration does not settle the function returns false WITHOUT running the Jacobi
+// fall-back (which costs ~50 normal fits); the caller queues the hypothesis for a second pass.
+__host__ __device__ inline bool fit_hypothesis(const G& g, int C, int64_t N, int64_t M, const double* __restrict__ v,
                                                const double* __restrict__ n, const int32_t* __restrict__ sv,
                                                const int32_t* __restrict__ sm, const FitWs& ws, double* Rt_out,
-                                               bool fast = true) {
+                                               bool fast = true, bool defer = false) {
   const int nu = 3 * (RSX_S + C), ld = nu | 1, T0 = 3 * RSX_S;
   // ---- 1. gather the sample
   for (int idx = g.tid; idx < C * 30; idx += g.nt) {
@@ -175,6 +177,7 @@ __host__ __device__ inline void fit_hypothesis(const G& g, int C, int64_t N, int
     have_kb = arrow_null4(g, ws.H, ld, C, ws.R, aw, ws.kb, ws.iflag + 8);
     if (!have_kb && g.tid == 0) ws.iflag[8] = -1;
   }
+  if (!have_kb && defer) return false;           // uniform over the group
   if (!have_kb) {
     cta_jacobi(g, ws.H, ws.V, nu, ld, ws.cs, ws.iflag, 40);
     if (g.tid == 0) {
@@ -263,6 +266,7 @@ __host__ __device__ inline void fit_hypothesis(const G& g, int C, int64_t N, int
     Rt_out[idx] = j < 3 ? ws.R[9 * c + 3 * r + j] : ws.misc[9] * u[T0 + 3 * c + r] / ws.misc[8];
   }
   g.sync();
+  return true;
 }
 
 // ---------------------------------------------------------------------------------------------------
