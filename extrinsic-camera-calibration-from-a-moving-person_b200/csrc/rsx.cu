@@ -30,13 +30,18 @@ __global__ void __launch_bounds__(32 * FITW_WARPS)
 k_rsx_fit_warp(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
                const int32_t* __restrict__ samp_v, const int32_t* __restrict__ samp_m, int64_t H,
                double* __restrict__ Rt, unsigned long long* __restrict__ stats /*[4]: fall-backs, sweeps, work counter, deferred*/,
-               int32_t* __restrict__ deferred /*null: the warp runs the Jacobi fall-back itself*/) {
+               int32_t* __restrict__ deferred /*null: the warp runs the Jacobi fall-back itself*/,
+               double* h_global /*[warps of the grid][nu][ld] or null: H in shared memory too*/) {
   extern __shared__ __align__(16) double sm[];
   const int nu = 3 * (RSX_S + C), ld = nu | 1;
-  const size_t per_warp = (fit_ws_small_doubles(C) + 2 * (size_t)nu * ld + 1) & ~(size_t)1;
+  // The dense normal matrix H is written once and read once (the arrow solver copies its blocks out), so it lives in
+  // an L2-resident global slab per warp; the solver's workspace (V) stays in shared memory.  That takes a warp's
+  // shared memory from 36 to 22 KB at 4 cameras: 10 resident warps per SM instead of 6 for a latency-bound kernel.
+  const size_t per_warp = (fit_ws_small_doubles(C) + (h_global ? 1 : 2) * (size_t)nu * ld + 1) & ~(size_t)1;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   FitWs ws;
-  fit_ws_carve(sm + warp * per_warp, nullptr, C, ws);
+  fit_ws_carve(sm + warp * per_warp, nullptr, C, ws,
+               h_global ? h_global + ((size_t)blockIdx.x * FITW_WARPS + warp) * (size_t)nu * ld : nullptr);
   WarpCtx g{lane, 32};
   // hypotheses are handed out one at a time from a global counter: a fit's cost varies (sweep count, the rare Jacobi
   // fall-back is ~50x a normal fit), so a fixed stride leaves most SMs idle while the slowest warp finishes
@@ -241,13 +246,25 @@ int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, 
   const size_t small = fit_ws_small_doubles(C) * sizeof(double);
   const size_t hv = sizeof(double) * 2 * (size_t)nu * ld;
   {  // few cameras: one warp per hypothesis
-    const size_t per_warp = ((fit_ws_small_doubles(C) + 2 * (size_t)nu * ld + 1) & ~(size_t)1) * sizeof(double);
+    const bool hglob = h->fit_mode != 3;                            // env RSX_FIT_MODE=3: H in shared memory, as before
+    const size_t per_warp = ((fit_ws_small_doubles(C) + (hglob ? 1 : 2) * (size_t)nu * ld + 1) & ~(size_t)1) * sizeof(double);
     const size_t smem = per_warp * FITW_WARPS;
     if (h->fit_mode != 0 && smem <= 110 * 1024 && arrow_ws_doubles(C, 32) <= (size_t)nu * ld) {
-      const int per_sm = (int)((220 * 1024) / smem);
+      const int per_sm = (int)((226 * 1024) / (smem + 1024));       // 1 KB per resident CTA is reserved by the system
       int64_t grid = (H + FITW_WARPS - 1) / FITW_WARPS;
       const int64_t cap = (int64_t)h->sm_count * per_sm;          // resident CTAs only: work is handed out dynamically
       if (grid > cap) grid = cap;
+      double* hg = nullptr;
+      if (hglob) {
+        const size_t need = sizeof(double) * (size_t)nu * ld * FITW_WARPS * (size_t)cap;
+        if (need > h->fit_scratch_bytes) {
+          if (h->fit_scratch) cudaFree(h->fit_scratch);
+          h->fit_scratch = nullptr; h->fit_scratch_bytes = 0;
+          BAX_CUDA(cudaMalloc(&h->fit_scratch, need));
+          h->fit_scratch_bytes = need;
+        }
+        hg = h->fit_scratch;
+      }
       BAX_CUDA(cudaMemsetAsync((unsigned long long*)h->fit_stats + 2, 0, 2 * sizeof(unsigned long long), s));
       BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_warp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       int32_t* deferred = nullptr;
@@ -262,7 +279,7 @@ int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, 
       }
       RsxTimer t(h, RSX_T_FIT, s, deferred ? 2 : 1);
       k_rsx_fit_warp<<<(unsigned)grid, 32 * FITW_WARPS, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt,
-                                                                   (unsigned long long*)h->fit_stats, deferred);
+                                                                   (unsigned long long*)h->fit_stats, deferred, hg);
       BAX_LAUNCH_CHECK();
       if (deferred) {
         BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_deferred, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(small + hv)));

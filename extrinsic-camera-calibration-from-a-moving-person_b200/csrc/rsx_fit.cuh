@@ -22,13 +22,15 @@ __host__ __device__ inline size_t fit_ws_small_doubles(int C) {      // everythi
   const int nu = 3 * (RSX_S + C);
   return (size_t)C * 30 * 3 + 9 * C + 2 * 110 + 2 * (nu / 2 + 1) + nu + 64 + 4 * nu + 8;
 }
-__host__ __device__ inline void fit_ws_carve(double* base, double* HV /*null: carve from base*/, int C, FitWs& ws) {
+__host__ __device__ inline void fit_ws_carve(double* base, double* HV /*null: carve from base*/, int C, FitWs& ws,
+                                             double* Hg = nullptr /*H alone in global memory, V carved from base*/) {
   const int nu = 3 * (RSX_S + C), ld = nu | 1;
   double* p = base;
   ws.vs = p; p += C * 30; ws.ns = p; p += C * 30; ws.w = p; p += C * 30; ws.R = p; p += 9 * C;
   ws.G = p; p += 110; ws.GV = p; p += 110; ws.cs = p; p += 2 * (nu / 2 + 1) + nu; ws.misc = p; p += 64; ws.kb = p; p += 4 * nu;
   ws.iflag = (int*)p; p += 8;
   if (HV) { ws.H = HV; ws.V = HV + (size_t)nu * ld; }
+  else if (Hg) { ws.H = Hg; ws.V = p; }
   else { ws.H = p; ws.V = p + (size_t)nu * ld; }
 }
 
