@@ -80,6 +80,9 @@ k_rsx_fit_deferred(int C, int64_t N, int64_t M, const double* __restrict__ v, co
   }
 }
 
+// Launch shape: 256 threads x 3 CTAs/SM (80 registers).  Measured alternatives at cfg2 (score pass of 100 k
+// hypotheses, 83.4 ms): 256x2 and 128x4 at 118 registers 92-96 ms, 128x7 at 72 registers 84.2, 512x1 97.8; taking a
+// thread's rays two at a time to interleave their chains (128 registers, 2 CTAs/SM) 92.2 -- no gain, dropped.
 __global__ void __launch_bounds__(SCORE_THREADS, 3)
 k_rsx_score(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
             const double* __restrict__ Rt, int64_t H, double* __restrict__ score, double* __restrict__ parts) {

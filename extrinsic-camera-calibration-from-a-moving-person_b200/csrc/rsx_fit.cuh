@@ -273,6 +273,27 @@ __host__ __device__ inline bool fit_hypothesis(const G& g, int C, int64_t N, int
 
 // ---------------------------------------------------------------------------------------------------
 // Score pieces of one model (calib_ransac.py:154-180), per-thread partial sums over a strided range.
+// reprojection error of the triangulated point X against ray i of every camera (calib_ransac.py:163-178), added to acc
+__host__ __device__ inline void score_ray(int C, int64_t M, const double* __restrict__ n, const double* Rt, int64_t i,
+                                          const double (&X)[4], double* e_out, const double* K00, double th2d,
+                                          uint8_t* mask2d, double& acc) {
+  bool inl = true;
+  for (int c = 0; c < C; ++c) {
+    const double* nn = n + ((size_t)c * M + i) * 3;
+    const double* P = Rt + 12 * c;
+    const double x0 = P[0] * X[0] + P[1] * X[1] + P[2] * X[2] + P[3] * X[3];
+    const double x1 = P[4] * X[0] + P[5] * X[1] + P[6] * X[2] + P[7] * X[3];
+    const double x2 = P[8] * X[0] + P[9] * X[1] + P[10] * X[2] + P[11] * X[3];
+    // one reciprocal instead of the reference's three divisions (calib_ransac.py:163-165); x2 / x2 is 1 or NaN
+    const double ix2 = 1.0 / x2;
+    const double e0 = x0 * ix2 - nn[0], e1 = x1 * ix2 - nn[1], e2 = ((x2 - x2) == 0.0 && x2 != 0.0 ? 1.0 : x2 * ix2) - nn[2];
+    acc += e0 * e0 + e1 * e1 + e2 * e2;
+    if (e_out) { double* o = e_out + ((size_t)i * C + c) * 3; o[0] = e0; o[1] = e1; o[2] = e2; }
+    if (mask2d) inl = inl && (K00[c] * sqrt(e0 * e0 + e1 * e1) <= th2d);
+  }
+  if (mask2d) mask2d[i] = inl ? 1 : 0;
+}
+
 //   Rt: [C][12] (shared);  returns sum over this thread's points of |e_ci|^2 (all cameras)
 template <class G>
 __host__ __device__ inline double score_points(const G& g, int C, int64_t M, const double* __restrict__ n,
@@ -289,21 +310,7 @@ __host__ __device__ inline double score_points(const G& g, int C, int64_t M, con
     }
     double X[4];
     eig4_smallest_fast(m, X);
-    bool inl = true;
-    for (int c = 0; c < C; ++c) {
-      const double* nn = n + ((size_t)c * M + i) * 3;
-      const double* P = Rt + 12 * c;
-      const double x0 = P[0] * X[0] + P[1] * X[1] + P[2] * X[2] + P[3] * X[3];
-      const double x1 = P[4] * X[0] + P[5] * X[1] + P[6] * X[2] + P[7] * X[3];
-      const double x2 = P[8] * X[0] + P[9] * X[1] + P[10] * X[2] + P[11] * X[3];
-      // one reciprocal instead of the reference's three divisions (calib_ransac.py:163-165); x2 / x2 is 1 or NaN
-      const double ix2 = 1.0 / x2;
-      const double e0 = x0 * ix2 - nn[0], e1 = x1 * ix2 - nn[1], e2 = ((x2 - x2) == 0.0 && x2 != 0.0 ? 1.0 : x2 * ix2) - nn[2];
-      acc += e0 * e0 + e1 * e1 + e2 * e2;
-      if (e_out) { double* o = e_out + ((size_t)i * C + c) * 3; o[0] = e0; o[1] = e1; o[2] = e2; }
-      if (mask2d) inl = inl && (K00[c] * sqrt(e0 * e0 + e1 * e1) <= th2d);
-    }
-    if (mask2d) mask2d[i] = inl ? 1 : 0;
+    score_ray(C, M, n, Rt, i, X, e_out, K00, th2d, mask2d, acc);
   }
   return acc;
 }
