@@ -146,3 +146,25 @@ def test_cfg2_pipeline_ransac_then_ba_refinement():
     ER1, Et1, Ep1, Ex1 = errors(R1, t1)
     assert np.mean(Ep1) < np.mean(Ep0) and np.mean(Ep1) < 6.0               # pixels; the noise alone is 3 px per axis
     assert np.max(ER1) < 0.03 and np.max(ER1) <= np.max(ER0) + 1e-3        # rad / sqrt(2)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["0", "2", "3"])
+def test_fit_kernel_modes_agree(monkeypatch, mode):
+    """RSX_FIT_MODE: 1 (default) warp-per-hypothesis fit with the normal matrix in a global slab and deferred Jacobi
+    fall-backs; 3 keeps the matrix in shared memory, 2 runs the fall-backs inline, 0 is the CTA Jacobi kernel.  Same
+    models up to the round-off of the two eigen-solvers: scores agree, same winner, same inlier masks."""
+    sc = scene.make_scene(C=4, N=40, seed=11, p_drop_2d=0.1, p_drop_3d=0.05)
+    v, n = cr.ransac_inputs(sc.p3d, sc.s3d, sc.p2d, sc.s2d, sc.K, OP_BONE)
+    th2, th3 = 50.0, 5.0 / 180 * np.pi
+    monkeypatch.delenv("RSX_FIT_MODE", raising=False)
+    (R0, t0, _), i0 = cr.calib_linear_ransac(v, n, sc.K, 64, th2, th3, 3, return_info=True, verbose=False)
+    monkeypatch.setenv("RSX_FIT_MODE", mode)
+    (R1, t1, _), i1 = cr.calib_linear_ransac(v, n, sc.K, 64, th2, th3, 3, return_info=True, verbose=False)
+    s0, s1 = i0["scores_local"].cpu().numpy(), i1["scores_local"].cpu().numpy()
+    ok = np.isfinite(s0)
+    assert np.array_equal(ok, np.isfinite(s1))
+    assert np.max(np.abs(s0[ok] - s1[ok]) / s0[ok]) < 1e-9
+    assert i0["best"] == i1["best"]
+    assert np.array_equal(i0["mask_2d"], i1["mask_2d"]) and np.array_equal(i0["mask_3d"], i1["mask_3d"])
+    assert np.max(np.abs(R0 - R1)) < 1e-8 and np.max(np.abs(t0 - t1)) < 1e-8
