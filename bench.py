@@ -95,6 +95,7 @@ def measured_peaks():
 
 
 _CPU_JOB = {}
+REF_PROCS = 8
 
 
 def _cpu_worker(reps):
@@ -127,7 +128,9 @@ def cpu_reference_leg(sc, inputs, w, budget_s=20.0, max_calls=8, procs=None):
     t0 = time.perf_counter()
     f = bo.objfun(theta, *args)                                   # one call alone: single-core figure + sizing
     t_one = time.perf_counter() - t0
-    procs = int(procs or os.cpu_count() or 1)
+    # a FIXED process count (not os.cpu_count()): the r01 arm forked one worker per core and its calls/s swung 9x
+    # between boxes / co-tenants as 32 workers fought for host DRAM
+    procs = int(procs or min(REF_PROCS, os.cpu_count() or 1))
     try:                                                          # stay inside the host memory: ~40 B x m per call
         import psutil
         procs = max(1, min(procs, int(psutil.virtual_memory().available * 0.5 / max(1.0, 60.0 * f.size * 8))))
@@ -153,6 +156,7 @@ def cpu_reference_leg(sc, inputs, w, budget_s=20.0, max_calls=8, procs=None):
                        f"{per_iter:.3g} s/iteration on {procs} cores ({(n_par + 1) * t_one:.3g} s on 1); dense SVD of the "
                        f"{f.size}x{n_par} Jacobian not included",
                 t_objfun_ms=t_one * 1e3, calls_per_s=calls_per_s, single_core_value=n_obs / ((n_par + 1) * t_one),
+                call_s_min_median_max=[float(np.min(times)), float(np.median(times)), float(np.max(times))],
                 n_obs=n_obs, host_cpus=os.cpu_count()), times
 
 
@@ -165,6 +169,10 @@ def run_reference(args):
     sc, inputs, w = make_workload(args.workload, 1000)
     t0 = time.perf_counter()
     leg, times = cpu_reference_leg(sc, inputs, w, budget_s=30.0, max_calls=max(1, args.steps))
+    if not args.no_cpu_rows:
+        # EXECUTED CPU rows (not extrapolated): the literal reference algorithm at frame counts it can run, and the
+        # strong non-reference row (analytic sparse Jacobian + LSMR) at cfg1 size
+        leg["executed"] = cpu_rows(budget_s=25.0)
     line = {"impl": "reference", "metric": "BA observations/s per LM iteration", "value": leg["value"],
             "unit": "observations/s", "n_gpus": args.gpus, "steps": len(times) // leg["cores"], "warmup": 1,
             "ms_per_step": float(np.mean(times)) * 1e3, "higher_is_better": True, "scaling": "weak",
@@ -348,6 +356,7 @@ def run_gpu(args):
     roofline = {"kernel": "k_rj (fused residual+Jacobian, bax_residual_jacobian)", "bound": "hbm",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_obs": 184.0 + 24.0 / cbar,
+                "in_timed_step": False,     # the LM step linearises with fused-accumulate kernels and never materialises J
                 "ms_per_launch": ms_rj, "obs_per_launch": n_obs_local, "obs_per_s": n_obs_local / (ms_rj * 1e-3)}
     prof = os.path.join(ROOT, "profiles", "rj_traffic.json")
     if os.path.isfile(prof):
@@ -364,6 +373,9 @@ def run_gpu(args):
     torch.cuda.synchronize()
     shares = {k: {"ms": round(v[0], 4), "launches": v[1]} for k, v in prob.timing_read().items() if v[1]}
     prob.timing(False)
+    # ---------------- the kernel that bounds the timed step: k_syrk96 (FP64 DMMA SYRK of the whitened Schur blocks)
+    roofline_step = syrk_roofline(prob, sol, ms_total / args.steps, C)
+    parity = sharded_parity_probe(rank, world, dev, group)
     comm = None
     if world > 1:      # device time inside the all-reduces (waiting for the slowest rank included), separate pass
         names = ["bone", "cost", "lin", "schur", "rhs2", "step", "norm", "gmax"]
@@ -407,7 +419,8 @@ def run_gpu(args):
                         "note": "every step: pinned-host observations + theta -> device, one full LM iteration "
                                 "(linearise, solves, cost evaluations), theta -> host; same solve-restart rule as value; the upload of step "
                                 "k+1 (second device buffer, copy stream) overlaps the kernels of step k"},
-                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "comm": comm,
+                "gpu_launches": int(launches), "roofline": roofline, "roofline_step": roofline_step,
+                "sharded_parity": parity, "cpu_baseline": cpu, "comm": comm,
                 "clocks": sampler.summary()}
     # ---------------- RANSAC leg (hypotheses/s), BASELINE configs[1]
     from calib_b200 import calib_ransac as cr
@@ -427,6 +440,75 @@ def run_gpu(args):
     prob.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def fp64_peaks():
+    """FP64 peaks measured on this pool's B200 by tools/micro/fp64_peak.cu (tools/fp64_peak_json.py)."""
+    for rnd in ("r02",):
+        p = os.path.join(ROOT, "profiles", rnd, "fp64_peak.json")
+        if os.path.isfile(p):
+            with open(p) as f:
+                d = json.load(f)
+            return float(d["dmma_tflops"]), float(d["dfma_tflops"]), f"measured (profiles/{rnd}/fp64_peak.json)"
+    return 37.0, 34.0, "fallback (B200 datasheet FP64)"
+
+
+def syrk_roofline(prob, sol, ms_step, C):
+    """k_syrk96 against the FP64 tensor (DMMA) peak: timed live with CUDA events (the library's own per-family event
+    timers) over damped solves at the current linearisation, so the bucket holds only the trial SYRK (k_syrk96 + its two
+    split-K reduction kernels, microseconds).  Algorithmic flops = the lower triangle incl. diagonal of the
+    (6C+B+1)^2 product over K = 3P columns; issued = what the 96x96 tiles execute (padding + full diagonal tiles)."""
+    import torch
+    dmma, dfma, src = fp64_peaks()
+    n_red = 6 * C + 12 + 1
+    K = 3 * prob.P
+    nt = (6 * C + 95) // 96
+    tiles = nt * (nt + 1) // 2
+    issued = tiles * 96.0 * 96.0 * K * 2.0
+    algorithmic = n_red * (n_red + 1) / 2.0 * K * 2.0
+    alpha = 0.01 * sol.g_2 / max(sol.x_norm, 1e-300)
+    prob.timing(True)
+    reps = 6
+    for _ in range(reps):
+        prob.trial(alpha, False)
+    torch.cuda.synchronize()
+    t = prob.timing_read()
+    prob.timing(False)
+    ms = t["syrk"][0] / reps
+    return {"kernel": "k_syrk96 (FP64 DMMA SYRK of the whitened Schur blocks, one per damped solve)", "bound": "tensor",
+            "pipe": "fp64 mma.sync.m8n8k4 (tcgen05 has no FP64 kind)", "achieved": algorithmic / (ms * 1e-3) / 1e12,
+            "peak": dmma, "unit": "TFLOP/s", "frac": algorithmic / (ms * 1e-3) / 1e12 / dmma, "traffic": None,
+            "issued_tflops": issued / (ms * 1e-3) / 1e12, "issued_frac": issued / (ms * 1e-3) / 1e12 / dmma,
+            "dfma_peak": dfma, "peak_source": src, "flops_per_launch_algorithmic": algorithmic,
+            "flops_per_launch_issued": issued, "tiles_96x96": tiles, "k_columns": K, "reduced_size": n_red,
+            "ms_per_launch": ms, "launches_per_solve": t["syrk"][1] // reps, "share_of_step": ms / ms_step,
+            "in_timed_step": True}
+
+
+def sharded_parity_probe(rank, world, dev, group, C=16, frames=960, seed=4242):
+    """The SAME fixed scene and start on every N: its frames are sharded over the N ranks, the cost and gradient norm at
+    theta0 and the cost after two LM iterations are reported — they must agree between the N = 1, 2, 4, 8 lines of the
+    driver's scaling run (sharded-parity check riding on SCALE)."""
+    import calib_b200  # noqa: F401
+    from calib_b200 import ba, scene
+    sc = scene.make_scene(C=C, N=frames, seed=seed, score_mode="uniform", p_drop_2d=0.2, p_drop_3d=0.1)
+    sp2d, ss2d, sp3d, ss3d = scene.ba_inputs(sc)
+    per = frames // world
+    a, b = rank * per, (rank + 1) * per if rank < world - 1 else frames
+    prob = ba.BAProblem(sc.K, np.ascontiguousarray(sp2d[:, a:b]), np.ascontiguousarray(ss2d[:, a:b]),
+                        np.ascontiguousarray(sp3d[:, a:b]), np.ascontiguousarray(ss3d[:, a:b]), ba.OP_BONE, 3.0, 7.0,
+                        device=dev, group=group, n_frames_global=frames)
+    try:
+        x0 = prob.triangulate(sc.R_init, sc.t_init)
+        theta0 = ba.to_theta(sc.R_init, sc.t_init, x0.reshape(-1, 3))
+        sol = ba.TRFSolver(prob, theta0, ftol=0.0, xtol=0.0, gtol=0.0)
+        cost0, g0 = sol.cost, sol.g_2
+        sol.iterate(); sol.iterate()
+        out = {"scene": f"{C} cameras x {frames} frames x 17 joints, seed {seed}, lambda 3/7, frames sharded over {world} GPU(s)",
+               "cost0": cost0, "g_norm0": g0, "cost_after_2_iterations": sol.cost, "nfev": sol.nfev}
+    finally:
+        prob.close()
+    return out
 
 
 def ransac_cpu_leg(v, n, sn, sm, scores, budget_s=15.0):
@@ -506,7 +588,11 @@ def run_local_single(mine, ba):
 
 
 def run_cpu_rows(args):
-    """`--impl cpu_rows`: the CPU rows that stand beside the GPU numbers, on this box's host
+    print(json.dumps(cpu_rows(float(os.environ.get("CPU_ROWS_BUDGET_S", "60")))))
+
+
+def cpu_rows(budget_s=60.0):
+    """`--impl cpu_rows` and the `executed` object of cpu_baseline: the CPU rows that stand beside the GPU numbers, on this box's host
     cores.  literal: SciPy least_squares(trf, dense 2-point finite differences, dense SVD) on the oracle port of ba.objfun —
     what reference ba.py:187-206 runs — at frame counts small enough to execute.  strong: NOT the reference: the same
     objective with the oracle's analytic sparse Jacobian through least_squares(jac=..., tr_solver='lsmr') at the cfg1 size."""
@@ -515,7 +601,7 @@ def run_cpu_rows(args):
     from calib_b200 import scene
     from oracle import ba_oracle as bo
     out = {"host_cpus": os.cpu_count(), "literal": [], "strong": None}
-    budget = float(os.environ.get("CPU_ROWS_BUDGET_S", "60"))
+    budget = budget_s
     t_start = time.perf_counter()
     for N in (5, 10, 20, 40):
         if time.perf_counter() - t_start > budget:
@@ -553,7 +639,7 @@ def run_cpu_rows(args):
                      "obs_per_s_per_iteration": n_obs * res.njev / dt, "status": int(res.status),
                      "triangulation_s": t_tri,
                      "note": "analytic sparse Jacobian + LSMR trust-region solver; not what the reference runs"}
-    print(json.dumps(out))
+    return out
 
 
 
@@ -565,6 +651,7 @@ def main():
     ap.add_argument("--workload", default="cfg4shard", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference", "cpu_rows"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cpu-rows", dest="no_cpu_rows", action="store_true", help="reference arm: skip the executed CPU rows")
     ap.add_argument("--batch", type=int, default=64, help="problems per GPU of the sweep leg (0 = skip)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":

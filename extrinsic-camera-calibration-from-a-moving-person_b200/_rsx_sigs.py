@@ -14,7 +14,9 @@ SIGS = {
     "rsx_argmin": (i32, [vp, vp, i64, P_i64, P_f64, vp]),
     "rsx_winner_masks": (i32, [vp, vp, vp, f64, f64, vp, vp, vp, vp, P_i64, vp]),
     "rsx_calib_linear": (i32, [vp, vp, vp, vp, vp, P_i64, vp]),
+    "rsx_calib_linear_eigs": (i32, [vp, P_f64]),
     "rsx_triangulate": (i32, [vp, vp, vp, vp]),
+    "rsx_fit_stats": (i32, [vp, P_i64, vp]),
     "rsx_timing_enable": (i32, [vp, i32]),
     "rsx_timing_read": (i32, [vp, P_f64, P_i64]),
 }

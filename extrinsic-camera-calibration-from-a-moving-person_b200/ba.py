@@ -642,8 +642,20 @@ def trf_schur(prob, theta0, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None, verb
 _cache = {}
 
 
+def _fingerprint(a):
+    """Content hash of an array: the drop-ins below are called with the same constants thousands of times (SciPy's
+    finite differences), but a caller may also mutate an array in place between calls (the reference's own
+    joints2projections does, util.py:556-569) — identity of the object says nothing about its content."""
+    import hashlib
+    if a is None:
+        return None
+    a = np.ascontiguousarray(a)
+    return (a.shape, a.dtype.str, hashlib.blake2b(a.view(np.uint8).reshape(-1), digest_size=16).digest())
+
+
 def _problem_for(K, sp2d, ss2d, sp3d, ss3d, bone_idx, C, N, J, lambda1, lambda2):
-    key = (id(K), id(sp2d), id(ss2d), id(sp3d), id(ss3d), C, N, J, float(lambda1), float(lambda2))
+    key = (_fingerprint(K), _fingerprint(sp2d), _fingerprint(ss2d), _fingerprint(sp3d), _fingerprint(ss3d),
+           _fingerprint(np.asarray(bone_idx)), C, N, J, float(lambda1), float(lambda2))
     hit = _cache.get("p")
     if hit is not None and hit[0] == key:
         return hit[1]
@@ -651,7 +663,7 @@ def _problem_for(K, sp2d, ss2d, sp3d, ss3d, bone_idx, C, N, J, lambda1, lambda2)
         hit[1].close()
     prob = BAProblem(K, np.asarray(sp2d).reshape(C, N * J, 2), np.asarray(ss2d).reshape(C, N, J), sp3d, ss3d,
                      bone_idx, lambda1, lambda2)
-    _cache["p"] = (key, prob, (K, sp2d, ss2d, sp3d, ss3d))     # keep the arrays alive: the key uses id()
+    _cache["p"] = (key, prob)
     return prob
 
 
@@ -684,8 +696,19 @@ def ba_main(camid, K, R_w2c, t_w2c, sp2d, ss2d, sp3d, ss3d, lambda1, lambda2, *,
         if verbose:
             f0 = prob.residual(theta0).cpu().numpy()
             e1 = f0[:2 * prob.n_vis]
-            e2 = f0[2 * prob.n_vis:2 * prob.n_vis + prob.n_v3d] / (lambda1 if lambda1 != 0 else 1.0)
-            e3 = f0[2 * prob.n_vis + prob.n_v3d:] / (lambda2 if lambda2 != 0 else 1.0)
+            if lambda1 == 0 or lambda2 == 0:
+                # the reference prints the UNSCALED prior terms (ba.py:179-183); with a zero weight they cannot be
+                # recovered from the weighted residual, so evaluate them once with unit weights
+                unit = BAProblem(K, np.asarray(sp2d).reshape(C, N * J, 2), ss2d, sp3d, ss3d, OP_BONE, 1.0, 1.0)
+                try:
+                    f1 = unit.residual(theta0).cpu().numpy()
+                finally:
+                    unit.close()
+                e2 = f1[2 * prob.n_vis:2 * prob.n_vis + prob.n_v3d]
+                e3 = f1[2 * prob.n_vis + prob.n_v3d:]
+            else:
+                e2 = f0[2 * prob.n_vis:2 * prob.n_vis + prob.n_v3d] / lambda1
+                e3 = f0[2 * prob.n_vis + prob.n_v3d:] / lambda2
             print(f"Initial mean NLL: {np.mean(e1 * e1)}")
             print(f"Initial mean 3D variance: {np.mean(e2 * e2)}")
             print(f"Initial mean bone-length variance: {np.mean(e3 * e3)}")

@@ -22,8 +22,9 @@ def calib_linear(v_CxNx3, n_CxMx3):
     prob = RansacProblem(v_CxNx3, n_CxMx3)
     try:
         R, t, _, info = prob.calib_linear(want_X=False)
-        if not info["converged"]:
-            print("WARN: degenerate case (only 4 eigenvalues should be zero)")      # calib_linear.py:99-101
+        w = np.array(info["eigs"])
+        if w[3] / w[4] > 1e-4:                                                   # calib_linear.py:98-100
+            print(f"WARN: degenerate case (only 4 eigenvalues should be zero): lambda={w}")
         X4 = prob.triangulate(R, t)
     finally:
         prob.close()

@@ -68,12 +68,13 @@ __global__ void __launch_bounds__(FIT_THREADS)
 k_rsx_fit_deferred(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
                    const int32_t* __restrict__ samp_v, const int32_t* __restrict__ samp_m,
                    const int32_t* __restrict__ deferred, const unsigned long long* __restrict__ stats,
-                   double* __restrict__ Rt) {
+                   unsigned long long* __restrict__ stats_total, double* __restrict__ Rt) {
   extern __shared__ __align__(16) double sm[];
   FitWs ws;
   fit_ws_carve(sm, nullptr, C, ws);
   CtaCtx g{(int)threadIdx.x, (int)blockDim.x};
   const unsigned long long nd = stats[3];
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(stats_total, nd);      // cumulative count behind rsx_fit_stats
   for (unsigned long long i = blockIdx.x; i < nd; i += gridDim.x) {
     const int64_t h = deferred[i];
     fit_hypothesis(g, C, N, M, v, n, samp_v + h * RSX_S, samp_m + h * RSX_S, ws, Rt + (size_t)h * C * 12, false);
@@ -193,8 +194,8 @@ extern "C" int rsx_create(int device, rsx_handle** out) {
     if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
   }
   { const char* e = getenv("RSX_FIT_MODE"); h->fit_mode = e ? atoi(e) : 1; }   // 0: CTA Jacobi kernel only
-  BAX_CUDA(cudaMalloc(&h->fit_stats, 4 * sizeof(unsigned long long)));
-  BAX_CUDA(cudaMemset(h->fit_stats, 0, 4 * sizeof(unsigned long long)));
+  BAX_CUDA(cudaMalloc(&h->fit_stats, 8 * sizeof(unsigned long long)));
+  BAX_CUDA(cudaMemset(h->fit_stats, 0, 8 * sizeof(unsigned long long)));
   h->bx = (bax_handle*)calloc(1, sizeof(bax_handle));
   h->bx->device = device; h->bx->sm_count = h->sm_count;
   *out = h;
@@ -245,6 +246,7 @@ static int ensure_models(rsx_handle* h, int64_t H) {
 }
 
 int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, int64_t H, double* Rt, cudaStream_t s) {
+  h->fits_total += H;
   const int C = h->C, nu = 3 * (RSX_S + C), ld = nu | 1;
   const size_t small = fit_ws_small_doubles(C) * sizeof(double);
   const size_t hv = sizeof(double) * 2 * (size_t)nu * ld;
@@ -287,7 +289,8 @@ int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, 
       if (deferred) {
         BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_deferred, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(small + hv)));
         k_rsx_fit_deferred<<<2 * h->sm_count, FIT_THREADS, small + hv, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, deferred,
-                                                                          (const unsigned long long*)h->fit_stats, Rt);
+                                                                          (const unsigned long long*)h->fit_stats,
+                                                                          (unsigned long long*)h->fit_stats + 4, Rt);
         BAX_LAUNCH_CHECK();
       }
       return BAX_OK;
@@ -384,6 +387,17 @@ extern "C" int rsx_triangulate(rsx_handle* h, const double* Rt, double* X4_out, 
   RsxTimer t(h, RSX_T_OTHER, s, 1);
   k_rsx_triangulate<<<grid, 256, sizeof(double) * 12 * h->C, s>>>(h->C, h->M, h->n, Rt, X4_out);
   BAX_LAUNCH_CHECK();
+  return BAX_OK;
+}
+
+extern "C" int rsx_fit_stats(rsx_handle* h, int64_t* out_host, void* stream) {
+  if (!h || !out_host) { bax_set_error("rsx_fit_stats: bad argument"); return BAX_E_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  BAX_CUDA(cudaSetDevice(h->device));
+  unsigned long long st[8];
+  BAX_CUDA(cudaMemcpyAsync(st, h->fit_stats, sizeof(st), cudaMemcpyDeviceToHost, s));
+  BAX_CUDA(cudaStreamSynchronize(s));
+  out_host[0] = h->fits_total; out_host[1] = (int64_t)st[0]; out_host[2] = (int64_t)st[4]; out_host[3] = (int64_t)st[1];
   return BAX_OK;
 }
 

@@ -60,8 +60,14 @@ def align(gR_w2c, gt_w2c, R_w2c, t_w2c, X3D):
     R2n = np.array([R_w2c[i] @ R.T for i in range(Cn)])
     Rc2w = np.array([R @ R_w2c[i].T for i in range(Cn)])
     t2n = np.array([s * R @ (-R_w2c[i].T @ t_w2c[i].reshape(3, 1)) + t.reshape(3, 1) for i in range(Cn)])
-    Rw2c = np.transpose(Rc2w, (0, 2, 1))                      # util.invRT_batch: inverse of [Rc2w | c]
-    tw2c = np.array([-Rw2c[i] @ t2n[i].reshape(3) for i in range(Cn)])
+    # util.invRT_batch (util.py:584-612): the inverse of the 4x4 [Rc2w | c; 0 1] by np.linalg.inv — NOT a transpose:
+    # linear_*/ransac_* cameras carry non-orthonormal R (calib_ransac.py:64-70) and run_all.sh evaluates them too
+    Rw2c, tw2c = np.empty((Cn, 3, 3)), np.empty((Cn, 3))
+    for i in range(Cn):
+        T = np.eye(4)
+        T[:3, :3], T[:3, 3] = Rc2w[i], t2n[i].reshape(3)
+        Ti = np.linalg.inv(T)
+        Rw2c[i], tw2c[i] = Ti[:3, :3], Ti[:3, 3]
     return Rw2c, tw2c[:, :, None], R2n, t2n, x3d_new.T
 
 

@@ -60,14 +60,26 @@ int rsx_winner_masks(rsx_handle* h, const double* Rt, const double* K00, double 
  * The 3(M_in + C) eigenproblem is never densified: rotations from the 3C x 3C Gram matrix; translations
  * from the 6 smallest eigenpairs of the arrow-structured normal matrix by block-eliminated inverse subspace
  * iteration with Rayleigh-Ritz.  Rt_out device [C][12]; X_out device [M_in][3] or NULL;
- * info_host[0..3] = { M_in, N_in, iterations, converged }. Synchronises. */
+ * info_host[0..3] = { M_in, N_in, iterations, converged }; a run that does not settle still returns its model with
+ * converged = 0 (the reference never fails here); BAX_E_NUMERIC only for a non-finite model. Synchronises. */
 int rsx_calib_linear(rsx_handle* h, const uint8_t* mask3d, const uint8_t* mask2d, double* Rt_out, double* X_out,
                      int64_t* info_host, void* stream);
+
+/* HOST: the 6 smallest eigenvalues (Ritz values, ascending) of the normal matrix from the last rsx_calib_linear on this
+ * handle — what the reference gets from eigh(subset_by_index=(0, 5)) and tests as w[3] / w[4] > 1e-4 for its
+ * "degenerate case" warning (calib_linear.py:94-100). */
+int rsx_calib_linear_eigs(rsx_handle* h, double* w_host /*[6]*/);
 
 /* DLT re-triangulation of all M ray sets under one model: calib_linear.py:127-133, i.e. pycalib.calib.triangulate
  * (identical code vendored at util.py:240-258) per point.  Rt device [C][12]; X4_out device [M][4]: the
  * dehomogenised point [x, y, z, 1], or the unit eigenvector itself where np.isclose(x[3], 0) (point at infinity). */
 int rsx_triangulate(rsx_handle* h, const double* Rt, double* X4_out, void* stream);
+
+/* Solver statistics of the minimal-sample fits since rsx_create (no reference counterpart: the reference's dense eigh
+ * at calib_ransac.py:96-98 never fails over).  out_host[0..3] = { hypotheses fitted, fits whose arrow-structured subspace
+ * iteration did not settle and were finished by the Jacobi diagonalisation, how many of those ran in the deferred
+ * second pass (k_rsx_fit_deferred), total sweeps of the arrow solver }.  Synchronises. */
+int rsx_fit_stats(rsx_handle* h, int64_t* out_host /*[4]*/, void* stream);
 
 /* timing hooks: CUDA-event ms and launch counts of { fit, score, final } since the last reset */
 int rsx_timing_enable(rsx_handle* h, int on);

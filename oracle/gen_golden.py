@@ -66,6 +66,46 @@ def gen_ba(name, scene_kw, available_joints, lam1, lam2, run_main=False):
     print("wrote", name, "m =", f0.size, "n =", theta0.size)
 
 
+def gen_ba_tight(name, scene_kw, available_joints, lam1, lam2, max_nfev=300, jacs=("2-point", "3-point")):
+    """Converged-extrinsics golden: the reference's objfun under the reference's solver call
+    (ba.py:187-206) with ftol = xtol = gtol = 1e-14, plus the literal ba_main end point.  Stores inputs and end points
+    only (no dense FD Jacobian), so a 40-frame scene stays a small file."""
+    rb, _, ru = ref_shim.load()
+    from scipy.optimize import least_squares
+    sc = scene_mod.make_scene(**scene_kw)
+    sp2d, ss2d, sp3d, ss3d = scene_mod.ba_inputs(sc, available_joints)
+    C, N, J = ss2d.shape
+    x0 = ru.triangulate_with_conf(sp2d, ss2d, sc.K, sc.R_init, sc.t_init, ss2d > 0)
+    theta0 = rb.to_theta(sc.R_init, sc.t_init, x0.reshape(-1, 3))
+    args = (sc.K, sp2d.reshape(C, N * J, 2), ss2d, sp3d, ss3d, ru.OP_BONE, C, N, J, lam1, lam2)
+    f0 = rb.objfun(theta0, *args)
+    out = dict(K=sc.K, R_init=sc.R_init, t_init=sc.t_init, sp2d=sp2d, ss2d=ss2d, sp3d=sp3d, ss3d=ss3d,
+               lam1=lam1, lam2=lam2, x0=x0, theta0=theta0, f0=f0, scene_kw=str(scene_kw), versions=str(versions()))
+    with quiet():
+        R, t, x = rb.ba_main(sc.camid, sc.K, sc.R_init, sc.t_init, sp2d, ss2d, sp3d, ss3d, lam1, lam2)
+    out.update(R_lit=R, t_lit=t)
+    for jac in jacs:
+        tag = "tight2" if jac == "2-point" else "tight3"
+        res = least_squares(rb.objfun, theta0, method="trf", jac=jac, ftol=1e-14, xtol=1e-14, gtol=1e-14,
+                            max_nfev=max_nfev, args=args)
+        R, t, x = rb.from_theta(res.x, C)
+        out.update({f"R_{tag}": R, f"t_{tag}": t, f"cost_{tag}": res.cost, f"nfev_{tag}": res.nfev,
+                    f"optimality_{tag}": res.optimality, f"theta_{tag}": res.x})
+        print(name, tag, "nfev", res.nfev, "cost", res.cost, "optimality", res.optimality, flush=True)
+    np.savez_compressed(os.path.join(OUT, f"ba_{name}.npz"), **out)
+    print("wrote", name, "m =", f0.size, "n =", theta0.size, flush=True)
+
+
+TIGHT_CASES = {
+    # name: (scene_kw, joints, lambda1, lambda2)   lambdas: run_synadl.sh / run_gafa.sh:3 / run_panoptic.sh:2
+    "partial_tight": (dict(C=5, N=8, seed=12, score_mode="uniform", p_drop_2d=0.3, p_drop_3d=0.1), 17, 3.0, 7.0),
+    "gafa_tight": (dict(C=3, N=7, seed=14, score_mode="uniform"), 17, 1.0, 1e5),
+    "panoptic_tight": (dict(C=6, N=8, seed=15, score_mode="uniform", p_drop_2d=0.3, p_drop_3d=0.1, width=1920,
+                            height=1080, focal=1400.0), 17, 100.0, 1.0),
+    "n40_tight": (dict(C=4, N=40, seed=16), 17, 1.0, 1.0),
+}
+
+
 def gen_ransac(name, scene_kw, n_iter, seed, th_2d, th_3d_deg):
     _, rc, ru = ref_shim.load()
     sc = scene_mod.make_scene(**scene_kw)
@@ -165,6 +205,59 @@ def gen_cli(name="cli_c4"):
     print("wrote", name)
 
 
+def gen_save_mask(name="save_mask_c4"):
+    """Golden of the observation-mask writer: the reference's own ba.save_mask (ba.py:235-266) on
+    the cli_c4 files with a handful of gross 2-D outliers injected, cameras = the scene's perturbed start.  Stores the
+    scores and poses the reference wrote to 2d_joint_mask/*.json (NaN = masked)."""
+    import json
+    import tempfile
+    dataio = importlib.import_module("extrinsic-camera-calibration-from-a-moving-person_b200.dataio")
+    rb, _, ru = ref_shim.load()
+    kw = dict(C=4, N=24, seed=31, p_drop_2d=0.1, p_drop_3d=0.05)
+    sc = scene_mod.make_scene(**kw)
+    rng = np.random.default_rng(77)
+    out_idx = np.stack([rng.integers(0, sc.C, 40), rng.integers(0, sc.N, 40), rng.integers(0, 25, 40)], axis=1)
+    out_off = rng.normal(0, 40.0, (40, 2))            # px; some beyond, some within the 20 px threshold
+    for (c, f, j), d in zip(out_idx, out_off):
+        sc.p2d[c, f, j] += d
+    aid, pid, gid, th_mask = 23, 102, 3, 20
+    R, t = sc.R_init, sc.t_init.reshape(-1, 3, 1)
+    scores, poses = [], []
+    with tempfile.TemporaryDirectory() as tmp:
+        d = os.path.join(tmp, "noise_3_0")
+        dataio.write_scene(d, sc, aid, pid, gid)
+        rb.PREFIX, rb.GID, rb.AID, rb.PID, rb.TH_MASK = d, gid, aid, pid, th_mask
+        with quiet():
+            rb.save_mask(sc.K, R, t, False, sc.width, sc.height)
+        for cid in sc.camid:
+            with open(os.path.join(d, "2d_joint_mask", f"A{aid:03d}_P{pid:03d}_G{gid:03d}_C{int(cid):03d}.json")) as fp:
+                data = json.load(fp)["data"]
+            scores.append([fr["skeleton"][0]["score"] for fr in data])
+            poses.append([fr["skeleton"][0]["pose"] for fr in data])
+            frames = [fr["frame_index"] for fr in data]
+    scores, poses = np.array(scores, dtype=np.float64), np.array(poses, dtype=np.float64)
+    np.savez_compressed(os.path.join(OUT, f"{name}.npz"), scene_kw=str(kw), out_idx=out_idx, out_off=out_off, aid=aid,
+                        pid=pid, gid=gid, th_mask=th_mask, R=R, t=t, scores=scores, poses=poses, frames=np.array(frames),
+                        versions=str(versions()))
+    print("wrote", name, "masked", int(np.isnan(scores).sum()), "of", scores.size)
+
+
+def gen_to_theta(name="to_theta_nonortho"):
+    """ba.to_theta / from_theta (ba.py:18-31, cv2.Rodrigues) on NON-orthonormal rotations — what linear_*/ransac_*.json
+    carry (calib_ransac.py:64-70): the reference's own theta and the R it unpacks again."""
+    rb, _, ru = ref_shim.load()
+    gl = np.load(os.path.join(OUT, "linear_c4.npz"))
+    gr = np.load(os.path.join(OUT, "ransac_c4.npz"))
+    Rs = np.concatenate([gl["R_linear"], gr["R_fin"], gr["R_hyp"][:4].reshape(-1, 3, 3)])
+    ts = np.concatenate([gl["t_linear"].reshape(-1, 3, 1), gr["t_fin"].reshape(-1, 3, 1), gr["t_hyp"][:4].reshape(-1, 3, 1)])
+    x = np.random.default_rng(5).normal(size=(7, 3))
+    theta = rb.to_theta(Rs, ts, x)
+    R2, t2, x2 = rb.from_theta(theta, len(Rs))
+    np.savez_compressed(os.path.join(OUT, f"{name}.npz"), R=Rs, t=ts, x=x, theta=theta, R_back=R2, t_back=t2, x_back=x2,
+                        versions=str(versions()))
+    print("wrote", name, "max |RR^T - I| =", np.max(np.abs(Rs @ Rs.transpose(0, 2, 1) - np.eye(3))))
+
+
 def gen_linear(name="linear_c4"):
     """File-level golden of the non-RANSAC linear calibration: the cli_c4 scene pushed through the reference's
     own calib_linear.main_linear (calib_linear.py:138-215)."""
@@ -205,7 +298,7 @@ def gen_linear(name="linear_c4"):
     print("wrote", name)
 
 
-def gen_eval(name="eval_c4"):
+def gen_eval(name="eval_c4", cams="init"):
     """Golden of the evaluation metrics: the reference's own eval.align / eval.calc_repro_error / util.eval_R /
     util.eval_t / util.triangulate_with_conf, strung together as eval.eval_main does (eval.py:126-150), plus the
     JSON summary eval_main writes.  pycalib.calib.absolute_orientation is not installable here: it is stubbed with
@@ -241,6 +334,10 @@ def gen_eval(name="eval_c4"):
     gp3d_w = np.array(sc.X_w)
     gt = sc.t_gt.reshape(-1, 3, 1)
     R, t = sc.R_init, sc.t_init.reshape(-1, 3, 1)
+    if cams == "linear":       # non-orthonormal R, as run_all.sh feeds eval.py with linear_*/ransac_*.json
+        gl = np.load(os.path.join(OUT, "linear_c4.npz"))
+        R, t = gl["R_linear"], gl["t_linear"].reshape(-1, 3, 1)
+        # the linear model lives in camera 0's frame at unit baseline: evaluate it as eval.py would, as is
     with quiet():
         x_all = ru.triangulate_with_conf(gp2d, gs2d, sc.K, R, t, (gs2d > 0))
         N, J = x_all.shape[:2]
@@ -256,14 +353,32 @@ def gen_eval(name="eval_c4"):
             re_.eval_main(sc.K, R, t, sc.R_gt, gt, gp2d, gs2d, gp3d_w, frame_skip, width, height, jo, scale)
             summary = open(jo).read()
     np.savez_compressed(os.path.join(OUT, f"{name}.npz"), scene_kw=str(kw), frame_skip=frame_skip, scale=scale,
-                        E_R=E_R, E_t=E_t, E_p=E_p, E_x=E_x, nR=nR, nt=nt, summary=summary, versions=str(versions()))
+                        E_R=E_R, E_t=E_t, E_p=E_p, E_x=E_x, nR=nR, nt=nt, summary=summary, R=R, t=t, versions=str(versions()))
     print("wrote", name)
 
 
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if len(sys.argv) > 2 and sys.argv[1] == "tight":
+        kw, nj, l1, l2 = TIGHT_CASES[sys.argv[2]]
+        big = kw["N"] >= 40
+        gen_ba_tight(sys.argv[2], kw, list(range(nj)), l1, l2, max_nfev=150 if big else 300,
+                     jacs=("3-point",) if big else ("2-point", "3-point"))
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "ransac_long":
+        # long enough to meet ill-conditioned minimal samples (the reference never rejects them,
+        # calib_ransac.py:99-104): exercises the deferred Jacobi fall-back of the CUDA fit
+        gen_ransac("c4_long", dict(C=4, N=40, seed=21, p_drop_2d=0.1, p_drop_3d=0.05), 1500, 0, 50.0, 5.0)
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "to_theta":
+        gen_to_theta()
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "save_mask":
+        gen_save_mask()
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "eval":
         gen_eval()
+        gen_eval("eval_c4_linear", "linear")
         return
     if len(sys.argv) > 1 and sys.argv[1] == "linear":
         gen_linear()
@@ -282,6 +397,14 @@ def main():
     gen_cli()
     gen_linear()
     gen_eval()
+    gen_eval('eval_c4_linear', 'linear')
+    gen_save_mask()
+    gen_to_theta()
+    for nm, (kw, nj, l1, l2) in TIGHT_CASES.items():
+        big = kw['N'] >= 40
+        gen_ba_tight(nm, kw, list(range(nj)), l1, l2, max_nfev=150 if big else 300,
+                     jacs=('3-point',) if big else ('2-point', '3-point'))
+    gen_ransac('c4_long', dict(C=4, N=40, seed=21, p_drop_2d=0.1, p_drop_3d=0.05), 1500, 0, 50.0, 5.0)
 
 
 if __name__ == "__main__":

@@ -206,3 +206,28 @@ def test_emulated_fit_score_masks_vs_reference_golden(emu, golden_dir, case):
     emu.emu_score(Cn, C.c_longlong(N), C.c_longlong(M), dp(v), dp(n), dp(models[best][1]), dp(parts), None, None, dp(K00),
                   C.c_double(float(g["th_2d"])), C.c_double(float(g["th_3d"])), m2.ctypes.data_as(pu), m3.ctypes.data_as(pu))
     assert np.array_equal(m2.astype(bool), g["mask_2d"]) and np.array_equal(m3.astype(bool), g["mask_3d"])
+
+
+def test_package_to_theta_vs_reference_on_non_orthonormal_rotations(golden_dir):
+    """calib_b200.ba.to_theta / from_theta (the PACKAGE's host functions, not the oracle's) against the reference's
+    ba.to_theta / from_theta (ba.py:18-31) on the non-orthonormal R of linear_*/ransac_* models: cv2.Rodrigues
+    projects them on SO(3) by SVD first (oracle/gen_golden.py gen_to_theta)."""
+    from calib_b200 import ba
+    g = np.load(os.path.join(golden_dir, "to_theta_nonortho.npz"))
+    assert np.max(np.abs(g["R"] @ g["R"].transpose(0, 2, 1) - np.eye(3))) > 1e-3      # really non-orthonormal
+    th = ba.to_theta(g["R"], g["t"], g["x"])
+    assert th.shape == g["theta"].shape and np.max(np.abs(th - g["theta"])) < 1e-12
+    R, t, x = ba.from_theta(g["theta"], len(g["R"]))
+    assert np.max(np.abs(R - g["R_back"])) < 1e-12 and np.array_equal(t, g["t_back"]) and np.array_equal(x, g["x_back"])
+
+
+@pytest.mark.parametrize("case", ["eval_c4", "eval_c4_linear"])
+def test_eval_align_vs_reference_golden(golden_dir, case):
+    """eval.align (eval.py:29-63) around the (unpinned) absolute_orientation: aligned cameras equal to the reference's,
+    including util.invRT_batch's 4x4 inverse for the non-orthonormal R of linear_*.json."""
+    import ast
+    from calib_b200 import eval as ev, scene
+    g = np.load(os.path.join(golden_dir, f"{case}.npz"))
+    sc = scene.make_scene(**ast.literal_eval(str(g["scene_kw"])))
+    nR, nt, _, _, _ = ev.align(sc.R_gt, sc.t_gt.reshape(-1, 3, 1), g["R"], g["t"], np.zeros((1, 3)))
+    assert np.max(np.abs(nR - g["nR"])) < 1e-12 and np.max(np.abs(nt - g["nt"])) < 1e-12

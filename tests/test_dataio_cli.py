@@ -131,15 +131,16 @@ def test_calib_linear_dropin_vs_reference_golden(golden_dir, tmp_path):
 
 
 @pytest.mark.gpu
-def test_eval_metrics_vs_reference_golden(golden_dir, tmp_path, capsys):
+@pytest.mark.parametrize("case", ["eval_c4", "eval_c4_linear"])
+def test_eval_metrics_vs_reference_golden(golden_dir, tmp_path, capsys, case):
     """eval.eval_main on the arrays the reference's own eval.align / calc_repro_error / util.eval_R / eval_t /
     triangulate_with_conf were run on (oracle/gen_golden.py gen_eval; pycalib.absolute_orientation restated there
     and here alike — that one function is unpinned): error vectors 1e-8 relative, identical JSON summary."""
-    g = np.load(os.path.join(golden_dir, "eval_c4.npz"))
+    g = np.load(os.path.join(golden_dir, f"{case}.npz"))     # _linear: non-orthonormal R (linear_*.json), util.invRT_batch
     sc = scene.make_scene(**ast.literal_eval(str(g["scene_kw"])))
     from calib_b200 import eval as ev
     jo = str(tmp_path / "e.json")
-    E_R, E_t, E_p, E_x = ev.eval_main(sc.K, sc.R_init, sc.t_init.reshape(-1, 3, 1), sc.R_gt, sc.t_gt.reshape(-1, 3, 1),
+    E_R, E_t, E_p, E_x = ev.eval_main(sc.K, g["R"], g["t"], sc.R_gt, sc.t_gt.reshape(-1, 3, 1),
                                       np.array(sc.p2d), np.array(sc.s2d), np.array(sc.X_w), int(g["frame_skip"]), 640, 360,
                                       jo, float(g["scale"]))
     for mine, ref in ((E_R, g["E_R"]), (E_t, g["E_t"]), (E_p, g["E_p"]), (E_x, g["E_x"])):
@@ -150,8 +151,35 @@ def test_eval_metrics_vs_reference_golden(golden_dir, tmp_path, capsys):
     assert "       Min  Median  Mean  Max" in out and "E_R:" in out and "E_x:" in out
     from calib_b200 import ba
     prob = ba.BAProblem(sc.K, np.array(sc.p2d), np.array(sc.s2d), None, None, ba.OP_BONE, 0.0, 0.0)
-    x_all = prob.triangulate(sc.R_init, sc.t_init)
+    x_all = prob.triangulate(g["R"], g["t"])
     prob.close()
     E_p2, x_gt_all, _, _ = ev.calc_repro_error(np.array(sc.s2d) > 0, int(g["frame_skip"]), x_all, np.array(sc.p2d), sc.K,
-                                               360, 640, sc.R_init, sc.t_init)
+                                               360, 640, g["R"], g["t"])
     assert np.allclose(E_p2, g["E_p"], rtol=1e-8, atol=1e-10) and x_gt_all.shape == np.array(sc.p2d).shape
+
+
+@pytest.mark.gpu
+def test_save_mask_vs_reference_golden(golden_dir, tmp_path):
+    """cli.save_mask against the files the reference's own ba.save_mask (ba.py:235-266) wrote for the same scene,
+    cameras and threshold (oracle/gen_golden.py gen_save_mask): which scores became NaN is bit-equal, every other
+    score and every pose value is identical, frame indices too."""
+    from calib_b200 import cli
+    g = np.load(os.path.join(golden_dir, "save_mask_c4.npz"))
+    sc = scene.make_scene(**ast.literal_eval(str(g["scene_kw"])))
+    for (c, f, j), d in zip(g["out_idx"], g["out_off"]):
+        sc.p2d[c, f, j] += d
+    aid, pid, gid = int(g["aid"]), int(g["pid"]), int(g["gid"])
+    d = str(tmp_path / "noise_3_0")
+    dataio.write_scene(d, sc, aid, pid, gid)
+    n_far = cli.save_mask(d, gid, aid, pid, sc.K, g["R"], g["t"], False, int(g["th_mask"]), sc.width, sc.height)
+    scores, poses = [], []
+    for cid in sc.camid:
+        fr, pose, score = dataio.load_poses(os.path.join(d, "2d_joint_mask", dataio.joint_file(aid, pid, gid, int(cid))))
+        assert np.array_equal(fr, g["frames"])
+        scores.append(score); poses.append(pose)
+    scores, poses = np.array(scores), np.array(poses)
+    assert scores.shape == g["scores"].shape and poses.shape == g["poses"].shape
+    assert np.array_equal(np.isnan(scores), np.isnan(g["scores"]))
+    assert int(np.isnan(g["scores"]).sum()) > 10 and n_far >= int(np.isnan(g["scores"]).sum()) - int(np.isnan(np.array(sc.s2d)).sum())
+    assert np.array_equal(np.nan_to_num(scores, nan=-1.0), np.nan_to_num(g["scores"], nan=-1.0))
+    assert np.array_equal(poses, g["poses"])

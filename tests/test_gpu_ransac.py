@@ -122,6 +122,53 @@ def test_cfg2_scale_properties():
     prob.close()
 
 
+def test_long_golden_exercises_the_deferred_fallback(golden_dir):
+    """1500 iterations of the unmodified reference loop (calib_ransac.py:147-207; oracle/gen_golden.py ransac_long):
+    long enough to meet ill-conditioned minimal samples, which the reference never rejects (:99-104) and which the
+    default CUDA fit hands to k_rsx_fit_deferred.  Gates: sample stream, winner and both masks bit-exact, final fit
+    1e-9; every model 1e-9; scores 1e-9 relative — except that a degenerate sample's score (hundreds of times the
+    winner's) amplifies eigen-solver round-off: those are held to 1e-8 and may be at most 0.2 % of the run; and the
+    run must really have gone through the deferred pass."""
+    g = np.load(os.path.join(golden_dir, "ransac_c4_long.npz"))
+    n_iter = int(g["n_iter"])
+    assert n_iter >= 1000
+    prob = cr.RansacProblem(g["vc"], g["n"])
+    (R, t, _), info = cr.calib_linear_ransac(g["vc"], g["n"], g["K"], n_iter, float(g["th_2d"]), float(g["th_3d"]),
+                                             int(g["seed"]), return_info=True, verbose=False, prob=prob)
+    st = info["fit_stats"]
+    assert st["fitted"] >= n_iter and st["fallbacks"] >= 1 and st["deferred"] >= 1, st
+    assert np.array_equal(info["sn"], g["sn"]) and np.array_equal(info["sm"], g["sm"])
+    assert info["best"] == int(g["best"])
+    assert np.array_equal(info["mask_2d"], g["mask_2d"]) and np.array_equal(info["mask_3d"], g["mask_3d"])
+    assert np.max(np.abs(R - g["R_fin"])) < 1e-9 and np.max(np.abs(t - g["t_fin"])) < 1e-9
+    s = info["scores_local"].cpu().numpy()
+    rel = np.abs(s - g["scores"]) / g["scores"]
+    near = g["scores"] < 50 * g["scores"].min()
+    assert np.max(rel[near]) < 1e-9
+    assert np.max(rel) < 1e-8 and np.count_nonzero(rel >= 1e-9) <= n_iter // 500, (np.max(rel), np.count_nonzero(rel >= 1e-9))
+    _, Rt = prob.fit_score(g["sn"].astype(np.int32), g["sm"].astype(np.int32), want_models=True)
+    Rt = Rt.cpu().numpy()
+    assert np.max(np.abs(Rt[:, :, :, :3] - g["R_hyp"])) < 1e-9
+    assert np.max(np.abs(Rt[:, :, :, 3:] - g["t_hyp"])) < 1e-9
+    prob.close()
+
+
+def test_cfg2_size_prefix_vs_oracle():
+    """BASELINE configs[1] size (N_o = 12000, M = 15000), first 200 hypotheses of seed 0 (SURVEY.md §8d "RANSAC"):
+    scores 1e-9 relative against the oracle, and the 200-hypothesis run — argmin, both inlier masks — bit-exact."""
+    sc = scene.cfg1(seed=2000)
+    v, n = cr.ransac_inputs(sc.p3d, sc.s3d, sc.p2d, sc.s2d, sc.K, OP_BONE)
+    th2, th3 = 50.0, 5.0 / 180 * np.pi
+    H = 200
+    (R, t, _), info = cr.calib_linear_ransac(v, n, sc.K, H, th2, th3, 0, return_info=True, verbose=False, final_fit=False)
+    (Ro, to, _), io = ro.calib_linear_ransac(v, n, sc.K, H, th2, th3, 0, return_info=True, final_fit=False)
+    assert np.array_equal(info["sn"], io["sn"]) and np.array_equal(info["sm"], io["sm"])
+    s = info["scores_local"].cpu().numpy()
+    assert np.max(np.abs(s - io["scores"]) / io["scores"]) < 1e-9
+    assert info["best"] == io["best"]
+    assert np.array_equal(info["mask_2d"], io["mask_2d"]) and np.array_equal(info["mask_3d"], io["mask_3d"])
+
+
 def test_cfg2_pipeline_ransac_then_ba_refinement():
     """BASELINE configs[1] end to end on the cfg1 scene (4 cameras x 1000 frames, sigma = 3 px): RANSAC linear
     calibration (20 000 of the 100 000 hypotheses, to keep the suite short), then ba.py's refinement started from its
