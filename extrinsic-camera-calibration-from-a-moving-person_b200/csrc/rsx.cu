@@ -84,7 +84,8 @@ k_rsx_fit_deferred(int C, int64_t N, int64_t M, const double* __restrict__ v, co
 // Launch shape: 256 threads x 3 CTAs/SM (80 registers).  Measured alternatives at cfg2 (score pass of 100 k
 // hypotheses, 83.4 ms): 256x2 and 128x4 at 118 registers 92-96 ms, 128x7 at 72 registers 84.2, 512x1 97.8; taking a
 // thread's rays two at a time to interleave their chains (128 registers, 2 CTAs/SM) 92.2 -- no gain, dropped.
-__global__ void __launch_bounds__(SCORE_THREADS, 3)
+template <int MODE, int MINB>
+__global__ void __launch_bounds__(SCORE_THREADS, MINB)
 k_rsx_score(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
             const double* __restrict__ Rt, int64_t H, double* __restrict__ score, double* __restrict__ parts) {
   extern __shared__ __align__(16) double sm[];       // [C][12] model, then 2*32 reduction scratch
@@ -96,7 +97,7 @@ k_rsx_score(int C, int64_t N, int64_t M, const double* __restrict__ v, const dou
     for (int i = threadIdx.x; i < 12 * C; i += blockDim.x) sRt[i] = Rt[(size_t)h * C * 12 + i];
     __syncthreads();
     double acc[2];
-    acc[0] = score_points(g, C, M, n, sRt, nullptr, nullptr, 0.0, nullptr);
+    acc[0] = score_points_sum<MODE>(g, C, M, n, sRt);
     acc[1] = score_dirs(g, C, N, v, sRt, nullptr, 0.0, nullptr);
     block_sum<2>(acc, red);
     if (threadIdx.x == 0) {
@@ -193,7 +194,8 @@ extern "C" int rsx_create(int device, rsx_handle** out) {
     cudaMemPool_t pool; unsigned long long keep = ~0ULL;
     if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
   }
-  { const char* e = getenv("RSX_FIT_MODE"); h->fit_mode = e ? atoi(e) : 1; }   // 0: CTA Jacobi kernel only
+  { const char* e = getenv("RSX_FIT_MODE"); h->fit_mode = e ? atoi(e) : 1; }
+  { const char* e = getenv("RSX_SCORE_MODE"); h->score_mode = e ? atoi(e) : 1; }   // 0: round-1 inverse iteration + per-camera divisions   // 0: CTA Jacobi kernel only
   BAX_CUDA(cudaMalloc(&h->fit_stats, 8 * sizeof(unsigned long long)));
   BAX_CUDA(cudaMemset(h->fit_stats, 0, 8 * sizeof(unsigned long long)));
   h->bx = (bax_handle*)calloc(1, sizeof(bax_handle));
@@ -331,7 +333,12 @@ extern "C" int rsx_fit_score(rsx_handle* h, const int32_t* samp_v, const int32_t
     const size_t smem = sizeof(double) * (((12 * h->C + 1) & ~1) + 2 * 32);
     int64_t grid = H < 64 * (int64_t)h->sm_count ? H : 64 * (int64_t)h->sm_count;
     RsxTimer t(h, RSX_T_SCORE, s, 1);
-    k_rsx_score<<<(unsigned)grid, SCORE_THREADS, smem, s>>>(h->C, h->N, h->M, h->v, h->n, models, H, score, parts);
+    if (h->score_mode == 0)
+      k_rsx_score<0, 3><<<(unsigned)grid, SCORE_THREADS, smem, s>>>(h->C, h->N, h->M, h->v, h->n, models, H, score, parts);
+    else if (h->score_mode == 2)
+      k_rsx_score<1, 2><<<(unsigned)grid, SCORE_THREADS, smem, s>>>(h->C, h->N, h->M, h->v, h->n, models, H, score, parts);
+    else
+      k_rsx_score<1, 3><<<(unsigned)grid, SCORE_THREADS, smem, s>>>(h->C, h->N, h->M, h->v, h->n, models, H, score, parts);
     BAX_LAUNCH_CHECK();
   }
   return BAX_OK;

@@ -294,6 +294,54 @@ __host__ __device__ inline void score_ray(int C, int64_t M, const double* __rest
   if (mask2d) mask2d[i] = inl ? 1 : 0;
 }
 
+// Sum-only variant for the RANSAC score pass (no error output, no masks): |e_ci|^2 = ((x0 - u x2)^2 + (x1 - v x2)^2) / x2^2
+// (the third component x2/x2 - 1 of calib_ransac.py:163-165 is 0 or one rounding, ~1e-32 in the sum), and the
+// per-camera quotients of up to four cameras are added over a common denominator, so a ray costs one FP64 division per
+// four cameras instead of one per camera (~10 instructions each).  x2 = 0 gives inf / NaN, which never wins (:182).
+__host__ __device__ inline void score_ray_sum(int C, int64_t M, const double* __restrict__ n, const double* Rt, int64_t i,
+                                              const double (&X)[4], double& acc) {
+  for (int c0 = 0; c0 < C; c0 += 4) {
+    double num = 0.0, den = 1.0;
+    const int c1 = c0 + 4 < C ? c0 + 4 : C;
+    for (int c = c0; c < c1; ++c) {
+      const double* nn = n + ((size_t)c * M + i) * 3;
+      const double* P = Rt + 12 * c;
+      const double x0 = P[0] * X[0] + P[1] * X[1] + P[2] * X[2] + P[3] * X[3];
+      const double x1 = P[4] * X[0] + P[5] * X[1] + P[6] * X[2] + P[7] * X[3];
+      const double x2 = P[8] * X[0] + P[9] * X[1] + P[10] * X[2] + P[11] * X[3];
+      const double d0 = x0 - nn[0] * x2, d1 = x1 - nn[1] * x2;
+      const double s = d0 * d0 + d1 * d1, q = x2 * x2;
+      num = num * q + s * den;
+      den = den * q;
+    }
+    acc += num / den;
+  }
+}
+
+//   MODE 1 (default): Rayleigh-quotient eigen-solver + common-denominator sum; MODE 0: round-1 arithmetic
+template <int MODE, class G>
+__host__ __device__ inline double score_points_sum(const G& g, int C, int64_t M, const double* __restrict__ n, const double* Rt) {
+  double acc = 0.0;
+  for (int64_t i = g.tid; i < M; i += g.nt) {
+    double m[10];
+#pragma unroll
+    for (int e = 0; e < 10; ++e) m[e] = 0.0;
+    for (int c = 0; c < C; ++c) {
+      const double* nn = n + ((size_t)c * M + i) * 3;
+      dlt_accumulate(Rt + 12 * c, nn[0], nn[1], m);
+    }
+    double X[4];
+    if (MODE == 1) {
+      eig4_smallest_rqi<false>(m, X);
+      score_ray_sum(C, M, n, Rt, i, X, acc);
+    } else {
+      eig4_smallest_invit(m, X);
+      score_ray(C, M, n, Rt, i, X, nullptr, nullptr, 0.0, nullptr, acc);
+    }
+  }
+  return acc;
+}
+
 //   Rt: [C][12] (shared);  returns sum over this thread's points of |e_ci|^2 (all cameras)
 template <class G>
 __host__ __device__ inline double score_points(const G& g, int C, int64_t M, const double* __restrict__ n,

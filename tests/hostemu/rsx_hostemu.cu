@@ -1,6 +1,7 @@
 // TEST INFRASTRUCTURE ONLY: runs the __host__ __device__ numerics of csrc/rsx_*.cuh on the CPU (one "thread",
 // syncs are no-ops) so the `-m "not gpu"` tests can check the device math against the oracle without a GPU.
 // Never linked into libbax.so, never imported by the package.
+#define RSX_HOST_STATS 1
 #include "../../extrinsic-camera-calibration-from-a-moving-person_b200/csrc/rsx_fit.cuh"
 #include <stdlib.h>
 #include <vector>
@@ -28,6 +29,18 @@ extern "C" void emu_eig4_fast(const double* A16, double* x4) {
   eig4_smallest_fast(m, x);
   for (int i = 0; i < 4; ++i) x4[i] = x[i];
 }
+extern "C" void emu_eig4_mode(const double* A16, double* x4, int mode, int norm) {
+  double m[10], x[4];
+  int e = 0;
+  for (int i = 0; i < 4; ++i) for (int j = i; j < 4; ++j) m[e++] = A16[4 * i + j];
+  if (mode == 0) eig4_smallest_invit(m, x);
+  else if (norm) eig4_smallest_rqi<true>(m, x);
+  else eig4_smallest_rqi<false>(m, x);
+  for (int i = 0; i < 4; ++i) x4[i] = x[i];
+}
+extern "C" void emu_rqi_stats(long long* out4, int reset) {
+  for (int i = 0; i < 4; ++i) { out4[i] = rsx_host_stats[i]; if (reset) rsx_host_stats[i] = 0; }
+}
 extern "C" void emu_fit(int C, long long N, long long M, const double* v, const double* n, const int* sv, const int* sm,
                         double* Rt_out) {
   const int nu = 3 * (RSX_S + C), ld = nu | 1;
@@ -46,6 +59,12 @@ extern "C" int emu_fit_mode(int C, long long N, long long M, const double* v, co
   CtaCtx g{0, 1};
   fit_hypothesis(g, C, N, M, v, n, sv, sm, ws, Rt_out, mode != 0);
   return ws.iflag[8];
+}
+extern "C" void emu_score_sum(int C, long long N, long long M, const double* v, const double* n, const double* Rt,
+                              double* parts2, int mode) {
+  CtaCtx g{0, 1};
+  parts2[0] = mode ? score_points_sum<1>(g, C, M, n, Rt) : score_points_sum<0>(g, C, M, n, Rt);
+  parts2[1] = score_dirs(g, C, N, v, Rt, nullptr, 0.0, nullptr);
 }
 extern "C" void emu_score(int C, long long N, long long M, const double* v, const double* n, const double* Rt,
                           double* parts2, double* e_out, double* e3d_out, const double* K00, double th2d, double th3d,
