@@ -26,22 +26,25 @@ k_rsx_fit(int C, int64_t N, int64_t M, const double* __restrict__ v, const doubl
 // steps, so FITW_WARPS hypotheses share a CTA, each with its own shared-memory workspace, and __syncwarp replaces the
 // CTA barrier.  A hypothesis whose iteration does not settle is finished by the same warp with the Jacobi solver.
 #define FITW_WARPS 2
-__global__ void __launch_bounds__(32 * FITW_WARPS)
+template <bool DEFER_ONLY>
+__global__ void __launch_bounds__(32 * FITW_WARPS, 8)
 k_rsx_fit_warp(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
                const int32_t* __restrict__ samp_v, const int32_t* __restrict__ samp_m, int64_t H,
                double* __restrict__ Rt, unsigned long long* __restrict__ stats /*[4]: fall-backs, sweeps, work counter, deferred*/,
                int32_t* __restrict__ deferred /*null: the warp runs the Jacobi fall-back itself*/,
-               double* h_global /*[warps of the grid][nu][ld] or null: H in shared memory too*/) {
+               double* h_global /*[warps of the grid][nu][ld] or null: H in shared memory too*/,
+               int compact /*compact shared-memory layout (needs deferred and h_global)*/) {
   extern __shared__ __align__(16) double sm[];
   const int nu = 3 * (RSX_S + C), ld = nu | 1;
   // The dense normal matrix H is written once and read once (the arrow solver copies its blocks out), so it lives in
   // an L2-resident global slab per warp; the solver's workspace (V) stays in shared memory.  That takes a warp's
   // shared memory from 36 to 22 KB at 4 cameras: 10 resident warps per SM instead of 6 for a latency-bound kernel.
-  const size_t per_warp = (fit_ws_small_doubles(C) + (h_global ? 1 : 2) * (size_t)nu * ld + 1) & ~(size_t)1;
+  const size_t per_warp = compact ? ((fit_ws_compact_small_doubles(C) + fit_ws_compact_v_doubles(C) + 1) & ~(size_t)1)
+                                  : ((fit_ws_small_doubles(C) + (h_global ? 1 : 2) * (size_t)nu * ld + 1) & ~(size_t)1);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   FitWs ws;
   fit_ws_carve(sm + warp * per_warp, nullptr, C, ws,
-               h_global ? h_global + ((size_t)blockIdx.x * FITW_WARPS + warp) * (size_t)nu * ld : nullptr);
+               h_global ? h_global + ((size_t)blockIdx.x * FITW_WARPS + warp) * (size_t)nu * ld : nullptr, compact != 0);
   WarpCtx g{lane, 32};
   // hypotheses are handed out one at a time from a global counter: a fit's cost varies (sweep count, the rare Jacobi
   // fall-back is ~50x a normal fit), so a fixed stride leaves most SMs idle while the slowest warp finishes
@@ -50,8 +53,8 @@ k_rsx_fit_warp(int C, int64_t N, int64_t M, const double* __restrict__ v, const 
     if (lane == 0) h = (long long)atomicAdd(stats + 2, 1ULL);
     h = __shfl_sync(0xffffffffu, h, 0);
     if (h >= H) break;
-    const bool done = fit_hypothesis(g, C, N, M, v, n, samp_v + h * RSX_S, samp_m + h * RSX_S, ws, Rt + (size_t)h * C * 12,
-                                     true, deferred != nullptr);
+    const bool done = fit_hypothesis_t<DEFER_ONLY>(g, C, N, M, v, n, samp_v + h * RSX_S, samp_m + h * RSX_S, ws,
+                                                   Rt + (size_t)h * C * 12, true, deferred != nullptr);
     if (lane == 0) {
       const int sw = ws.iflag[8];
       if (sw < 0) atomicAdd(stats, 1ULL); else atomicAdd(stats + 1, (unsigned long long)sw);
@@ -254,7 +257,10 @@ int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, 
   const size_t hv = sizeof(double) * 2 * (size_t)nu * ld;
   {  // few cameras: one warp per hypothesis
     const bool hglob = h->fit_mode != 3;                            // env RSX_FIT_MODE=3: H in shared memory, as before
-    const size_t per_warp = ((fit_ws_small_doubles(C) + (hglob ? 1 : 2) * (size_t)nu * ld + 1) & ~(size_t)1) * sizeof(double);
+    const bool defer_ok = h->fit_mode != 2 && small + hv <= 200 * 1024;
+    const bool compact = hglob && defer_ok && h->fit_mode != 5;   // env RSX_FIT_MODE=5: round-1 shared-memory layout
+    const size_t per_warp = (compact ? ((fit_ws_compact_small_doubles(C) + fit_ws_compact_v_doubles(C) + 1) & ~(size_t)1)
+                                     : ((fit_ws_small_doubles(C) + (hglob ? 1 : 2) * (size_t)nu * ld + 1) & ~(size_t)1)) * sizeof(double);
     const size_t smem = per_warp * FITW_WARPS;
     if (h->fit_mode != 0 && smem <= 110 * 1024 && arrow_ws_doubles(C, 32) <= (size_t)nu * ld) {
       const int per_sm = (int)((226 * 1024) / (smem + 1024));       // 1 KB per resident CTA is reserved by the system
@@ -273,7 +279,8 @@ int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, 
         hg = h->fit_scratch;
       }
       BAX_CUDA(cudaMemsetAsync((unsigned long long*)h->fit_stats + 2, 0, 2 * sizeof(unsigned long long), s));
-      BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_warp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_warp<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_warp<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       int32_t* deferred = nullptr;
       if (h->fit_mode != 2 && small + hv <= 200 * 1024) {          // env RSX_FIT_MODE=2: fall-backs inline, as before
         if (H > h->cap_deferred) {
@@ -285,8 +292,12 @@ int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, 
         deferred = h->deferred;
       }
       RsxTimer t(h, RSX_T_FIT, s, deferred ? 2 : 1);
-      k_rsx_fit_warp<<<(unsigned)grid, 32 * FITW_WARPS, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt,
-                                                                   (unsigned long long*)h->fit_stats, deferred, hg);
+      if (deferred)
+        k_rsx_fit_warp<true><<<(unsigned)grid, 32 * FITW_WARPS, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt,
+                                                                         (unsigned long long*)h->fit_stats, deferred, hg, compact ? 1 : 0);
+      else
+        k_rsx_fit_warp<false><<<(unsigned)grid, 32 * FITW_WARPS, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt,
+                                                                          (unsigned long long*)h->fit_stats, deferred, hg, 0);
       BAX_LAUNCH_CHECK();
       if (deferred) {
         BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_deferred, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(small + hv)));

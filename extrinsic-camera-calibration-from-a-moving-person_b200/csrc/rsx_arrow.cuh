@@ -32,26 +32,42 @@ struct ArrowWs {
 };
 __host__ __device__ inline size_t arrow_ws_doubles(int C, int nt) {
   const int nu = 3 * (RSX_S + C), n3 = 3 * C;
-  return 90 + (size_t)30 * n3 + (size_t)n3 * n3 + n3 + 2 * (size_t)nu * ARW_K + 16 * (size_t)nt + 32;
+  return 90 + (size_t)30 * n3 + (size_t)n3 * n3 + n3 + 2 * (size_t)nu * ARW_K + (nt == 32 ? 0 : 16 * (size_t)nt) + 32;   // a warp reduces by shuffles
 }
 __host__ __device__ inline void arrow_ws_carve(double* p, int C, int nt, ArrowWs& a) {
   const int nu = 3 * (RSX_S + C), n3 = 3 * C;
   a.Ld = p; p += 90; a.Wm = p; p += 30 * n3; a.S = p; p += n3 * n3; a.rS = p; p += n3;
-  a.Q = p; p += nu * ARW_K; a.Z = p; p += nu * ARW_K; a.red = p; p += 16 * nt; a.out = p;
+  a.Q = p; p += nu * ARW_K; a.Z = p; p += nu * ARW_K; a.red = p; p += (nt == 32 ? 0 : 16 * nt); a.out = p;
 }
 
-// out[j] = sum over the group of vals[j], j < k <= 16 (every thread reads the same out[] afterwards)
-template <class G>
-__host__ __device__ inline void group_sum(const G& g, const double* vals, int k, double* red, double* out) {
-  for (int j = 0; j < k; ++j) red[j * g.nt + g.tid] = vals[j];
+// vals[j] <- sum over the group of vals[j], j < K <= 16, in every thread.  One warp on the device: xor-butterfly of
+// shuffles (every lane ends with the bit-identical sum: a + b == b + a), no shared memory and no bank conflicts — the
+// [16][nt] scratch of the generic version was 4 KB per warp and its second phase a 16-way conflict.  Any other group
+// (CTA, host): through red[K][nt] / out[K] with two syncs.
+template <int K, class G>
+__host__ __device__ inline void group_allsum(const G& g, double (&vals)[K], double* red, double* out) {
+  for (int j = 0; j < K; ++j) red[j * g.nt + g.tid] = vals[j];
   g.sync();
-  for (int j = g.tid; j < k; j += g.nt) {
+  for (int j = g.tid; j < K; j += g.nt) {
     double s = 0.0;
+#pragma unroll 1
     for (int t = 0; t < g.nt; ++t) s += red[j * g.nt + t];
     out[j] = s;
   }
   g.sync();
+  for (int j = 0; j < K; ++j) vals[j] = out[j];
+  g.sync();                                              // out[] may be reused by the next call
 }
+#ifdef __CUDA_ARCH__
+template <int K>
+__device__ __forceinline__ void group_allsum(const WarpCtx& g, double (&vals)[K], double*, double*) {
+#pragma unroll
+  for (int m = 16; m >= 1; m >>= 1) {
+#pragma unroll
+    for (int j = 0; j < K; ++j) vals[j] += __shfl_xor_sync(0xffffffffu, vals[j], m);
+  }
+}
+#endif
 
 // Z <- orthonormal basis of span(Z) by Cholesky QR (Gram matrix -> 4x4 Cholesky -> Z R^-1); called twice per sweep,
 // the second pass removes the O(eps cond^2) loss of orthogonality of the first.  Returns false on a non-positive pivot.
@@ -65,10 +81,10 @@ __host__ __device__ inline bool cholqr4(const G& g, double* Z, int nu, double* r
     for (int a = 0; a < ARW_K; ++a)
       for (int b = a; b < ARW_K; ++b) p[e++] += z[a] * z[b];
   }
-  group_sum(g, p, 10, red, out);
+  group_allsum(g, p, red, out);
   // upper Cholesky factor R (Gram = R' R), computed redundantly by every thread
-  const double m00 = out[0], m01 = out[1], m02 = out[2], m03 = out[3], m11 = out[4], m12 = out[5], m13 = out[6],
-               m22 = out[7], m23 = out[8], m33 = out[9];
+  const double m00 = p[0], m01 = p[1], m02 = p[2], m03 = p[3], m11 = p[4], m12 = p[5], m13 = p[6],
+               m22 = p[7], m23 = p[8], m33 = p[9];
   if (!(m00 > 0)) return false;
   const double i0 = rsx_rsqrt(m00);
   const double r01 = m01 * i0, r02 = m02 * i0, r03 = m03 * i0;
@@ -83,7 +99,6 @@ __host__ __device__ inline bool cholqr4(const G& g, double* Z, int nu, double* r
   const double d3 = m33 - r03 * r03 - r13 * r13 - r23 * r23;
   if (!(d3 > 0)) return false;
   const double i3 = rsx_rsqrt(d3);
-  g.sync();                                              // everyone has read out[] before it is reused
   for (int i = g.tid; i < nu; i += g.nt) {               // row z <- z R^-1 (forward substitution along the row)
     double* z = Z + i * ARW_K;
     const double q0 = z[0] * i0;
@@ -96,18 +111,126 @@ __host__ __device__ inline bool cholqr4(const G& g, double* Z, int nu, double* r
   return true;
 }
 
+// Dominant 3-dimensional invariant subspace of the 10 x 10 Gram matrix of the stacked sample directions (the top-3
+// right singular vectors of the reference's SVD at calib_ransac.py:59-63 are V^T u_k / sigma_k; any basis of the
+// subspace serves, see fit_hypothesis).  Orthogonal iteration instead of the cyclic Jacobi diagonalisation of the whole
+// matrix (~9 rounds x 3 synchronised phases x 6-8 sweeps, a fifth of the fit's instructions): six steps with G^4
+// (contraction (s4/s3)^8 per step), then steps with G itself, Cholesky-QR twice, until the subspace moves by < 3e-15
+// (or sits on its round-off floor)
+// — G^4 only pre-conditions the start, the accuracy is that of iterating with G.  Returns false when it does not
+// settle (s3 ~ s4: a degenerate sample); the caller then runs / defers to the Jacobi path, so the result never depends
+// on this shortcut.  Gm: [10][11]; scr: 2 x 110 + 2 x 30 + 32 doubles (+ 16 nt unless one warp); U out: [10][3].
+#define TOP3_SCR_DOUBLES(nt) (2 * 110 + 2 * 32 + 32 + ((nt) == 32 ? 0 : 16 * (nt)))
+template <class G>
+__host__ __device__ inline bool cholqr3(const G& g, double* Y /*[10][3]*/, double* red, double* out) {
+  double p[6] = {0, 0, 0, 0, 0, 0};
+  for (int a = g.tid; a < 10; a += g.nt) {
+    const double y0 = Y[3 * a], y1 = Y[3 * a + 1], y2 = Y[3 * a + 2];
+    p[0] += y0 * y0; p[1] += y0 * y1; p[2] += y0 * y2; p[3] += y1 * y1; p[4] += y1 * y2; p[5] += y2 * y2;
+  }
+  group_allsum(g, p, red, out);
+  if (!(p[0] > 0)) return false;
+  const double i0 = rsx_rsqrt(p[0]);
+  const double r01 = p[1] * i0, r02 = p[2] * i0;
+  const double d1 = p[3] - r01 * r01;
+  if (!(d1 > 0)) return false;
+  const double i1 = rsx_rsqrt(d1);
+  const double r12 = (p[4] - r01 * r02) * i1;
+  const double d2 = p[5] - r02 * r02 - r12 * r12;
+  if (!(d2 > 0)) return false;
+  const double i2 = rsx_rsqrt(d2);
+  for (int a = g.tid; a < 10; a += g.nt) {
+    const double q0 = Y[3 * a] * i0;
+    const double q1 = (Y[3 * a + 1] - q0 * r01) * i1;
+    const double q2 = (Y[3 * a + 2] - q0 * r02 - q1 * r12) * i2;
+    Y[3 * a] = q0; Y[3 * a + 1] = q1; Y[3 * a + 2] = q2;
+  }
+  g.sync();
+  return true;
+}
+template <class G>
+__host__ __device__ inline bool top3_subspace(const G& g, const double* Gm, double* scr, double* Uout, int* iters_out) {
+  double* G2 = scr; double* G4 = scr + 110; double* U = scr + 220; double* Y = scr + 252; double* out = scr + 284;
+  double* red = scr + 316;
+  for (int idx = g.tid; idx < 100; idx += g.nt) {
+    const int a = idx / 10, b = idx - 10 * a;
+    double acc = 0.0;
+    for (int k = 0; k < 10; ++k) acc += Gm[a * 11 + k] * Gm[k * 11 + b];
+    G2[a * 11 + b] = acc;
+  }
+  for (int idx = g.tid; idx < 30; idx += g.nt) {
+    const unsigned hsh = (unsigned)(idx + 1) * 2654435761u;
+    U[idx] = (double)(hsh >> 8) * (1.0 / 16777216.0) - 0.5;
+  }
+  g.sync();
+  for (int idx = g.tid; idx < 100; idx += g.nt) {
+    const int a = idx / 10, b = idx - 10 * a;
+    double acc = 0.0;
+    for (int k = 0; k < 10; ++k) acc += G2[a * 11 + k] * G2[k * 11 + b];
+    G4[a * 11 + b] = acc;
+  }
+  if (!cholqr3(g, U, red, out)) return false;          // (syncs inside)
+  double prev = 1e300;
+  int it = 0;
+  for (; it < 48; ++it) {
+    const bool pre = it < 6;
+    const double* Mx = pre ? G4 : Gm;
+    for (int idx = g.tid; idx < 30; idx += g.nt) {
+      const int a = idx / 3, k = idx - 3 * a;
+      double acc = 0.0;
+      for (int b = 0; b < 10; ++b) acc += Mx[a * 11 + b] * U[3 * b + k];
+      Y[idx] = acc;
+    }
+    g.sync();
+    if (!cholqr3(g, Y, red, out)) return false;
+    if (pre) {
+      for (int idx = g.tid; idx < 30; idx += g.nt) U[idx] = Y[idx];
+      g.sync();
+      continue;
+    }
+    if (!cholqr3(g, Y, red, out)) return false;
+    // change of the subspace: || Y - U (U' Y) ||_F^2
+    double pm[9];
+    for (int e = 0; e < 9; ++e) pm[e] = 0.0;
+    for (int a = g.tid; a < 10; a += g.nt)
+      for (int p = 0; p < 3; ++p)
+        for (int q = 0; q < 3; ++q) pm[3 * p + q] += U[3 * a + p] * Y[3 * a + q];
+    group_allsum(g, pm, red, out);
+    double er[1] = {0.0};
+    for (int a = g.tid; a < 10; a += g.nt)
+      for (int q = 0; q < 3; ++q) {
+        double d = Y[3 * a + q];
+        for (int p = 0; p < 3; ++p) d -= U[3 * a + p] * pm[3 * p + q];
+        er[0] += d * d;
+      }
+    group_allsum(g, er, red, out);
+    const double err2 = er[0];
+    g.sync();
+    for (int idx = g.tid; idx < 30; idx += g.nt) U[idx] = Y[idx];
+    g.sync();
+    if (!(err2 == err2)) return false;
+    if (err2 < 1e-29 || (err2 < 1e-24 && err2 > 0.81 * prev)) { ++it; break; }
+    prev = err2;
+    if (it == 47) return false;
+  }
+  if (iters_out) *iters_out = it;
+  for (int idx = g.tid; idx < 30; idx += g.nt) Uout[idx] = U[idx];
+  g.sync();
+  return true;
+}
+
 // H: [nu][ld] dense symmetric (read only), R: [C][9] rotations (for the start vectors), kb: [nu][4] basis out.
 template <class G>
 __host__ __device__ inline bool arrow_null4(const G& g, const double* H, int ld, int C, const double* R,
-                                            const ArrowWs& a, double* kb, int* sweeps_out) {
+                                            const ArrowWs& a, double* kb, int* sweeps_out,
+                                            int max_sweeps = ARW_MAX_SWEEPS) {
   const int n3 = 3 * C, T0 = 3 * RSX_S, nu = T0 + n3;
   // ---- shift: far below lambda_1 (>= 1e-7 of the mean diagonal here), far above the round-off of the factorisation
   double tr[1] = {0.0};
   for (int i = g.tid; i < nu; i += g.nt) tr[0] += H[i * ld + i];
-  group_sum(g, tr, 1, a.red, a.out);
-  const double sig = 1e-13 * a.out[0] / nu;
+  group_allsum(g, tr, a.red, a.out);
+  const double sig = 1e-13 * tr[0] / nu;
   if (!(sig > 0)) return false;
-  g.sync();
   // ---- D_i + sig I = L_i L_i'
   for (int i = g.tid; i < RSX_S; i += g.nt) {
     const double* d = H + (3 * i) * ld + 3 * i;
@@ -137,6 +260,7 @@ __host__ __device__ inline bool arrow_null4(const G& g, const double* H, int ld,
     const int r = t / n3, c = t - r * n3;
     if (c > r) continue;
     double s = H[(T0 + r) * ld + T0 + c] + (r == c ? sig : 0.0);
+#pragma unroll 2
     for (int k = 0; k < 3 * RSX_S; ++k) s -= a.Wm[k * n3 + r] * a.Wm[k * n3 + c];
     a.S[r * n3 + c] = s;
   }
@@ -173,7 +297,7 @@ __host__ __device__ inline bool arrow_null4(const G& g, const double* H, int ld,
   double prev = 1e300;
   bool done = false;
   int sweep = 0;
-  for (; sweep < ARW_MAX_SWEEPS && !done; ++sweep) {
+  for (; sweep < max_sweeps && !done; ++sweep) {
     // ---- Z = (H + sig I)^-1 Q by block elimination
     for (int t = g.tid; t < RSX_S * ARW_K; t += g.nt) {            // y_i = L_i^-1 q_i
       const int i = t / ARW_K, v = t - i * ARW_K;
@@ -187,6 +311,7 @@ __host__ __device__ inline bool arrow_null4(const G& g, const double* H, int ld,
     for (int t = g.tid; t < n3 * ARW_K; t += g.nt) {               // r = q_t - W' y
       const int r = t / ARW_K, v = t - r * ARW_K;
       double s = a.Q[(T0 + r) * ARW_K + v];
+#pragma unroll 2
       for (int k = 0; k < 3 * RSX_S; ++k) s -= a.Wm[k * n3 + r] * a.Z[k * ARW_K + v];
       a.Z[(T0 + r) * ARW_K + v] = s;
     }
@@ -227,9 +352,7 @@ __host__ __device__ inline bool arrow_null4(const G& g, const double* H, int ld,
     for (int i = g.tid; i < nu; i += g.nt)
       for (int p = 0; p < ARW_K; ++p)
         for (int q = 0; q < ARW_K; ++q) gm[4 * p + q] += a.Q[i * ARW_K + p] * a.Z[i * ARW_K + q];
-    group_sum(g, gm, 16, a.red, a.out);
-    for (int e = 0; e < 16; ++e) gm[e] = a.out[e];
-    g.sync();
+    group_allsum(g, gm, a.red, a.out);
     double er[1] = {0.0};
     for (int i = g.tid; i < nu; i += g.nt)
       for (int q = 0; q < ARW_K; ++q) {
@@ -237,9 +360,8 @@ __host__ __device__ inline bool arrow_null4(const G& g, const double* H, int ld,
         for (int p = 0; p < ARW_K; ++p) d -= a.Q[i * ARW_K + p] * gm[4 * p + q];
         er[0] += d * d;
       }
-    group_sum(g, er, 1, a.red, a.out);
-    const double err2 = a.out[0];
-    g.sync();
+    group_allsum(g, er, a.red, a.out);
+    const double err2 = er[0];
     for (int i = g.tid; i < nu * ARW_K; i += g.nt) a.Q[i] = a.Z[i];
     g.sync();
     // settled: the subspace moved by less than 1e-12 (the error left is that times rho / (1 - rho)), or it sits on
@@ -247,7 +369,11 @@ __host__ __device__ inline bool arrow_null4(const G& g, const double* H, int ld,
 #if defined(ARW_DEBUG) && !defined(__CUDA_ARCH__)
     printf("  sweep %d err2 %.3e\n", sweep, err2);
 #endif
-    done = (err2 < 1e-24) || (err2 < 1e-21 && err2 > 0.81 * prev);
+    // what is LEFT after a movement of sqrt(err2) is that times rho / (1 - rho), rho^2 ~ err2 / prev the observed
+    // contraction: a slowly converging run (rho ~ 0.8, possible now that up to 160 sweeps are allowed) must move less
+    const double rho2 = err2 < prev ? err2 / prev : 1.0, omr = 1.0 - sqrt(rho2);
+    const double amp2 = rho2 > 0.25 ? rho2 / (omr * omr) : 1.0;
+    done = (err2 * amp2 < 1e-24) || (err2 < 1e-21 && err2 > 0.81 * prev);
     if (!(err2 == err2)) return false;                             // NaN
     prev = err2;
   }

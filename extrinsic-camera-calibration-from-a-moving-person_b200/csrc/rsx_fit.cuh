@@ -17,31 +17,60 @@ struct FitWs {
   double* misc;  // [64]
   double* kb;    // [nu][4]   basis of the 4 smallest eigen-directions of H
   int* iflag;    // [8]
+  size_t v_doubles;   // capacity of V (nu * ld, or the arrow workspace in the compact layout)
 };
 __host__ __device__ inline size_t fit_ws_small_doubles(int C) {      // everything but H, V
   const int nu = 3 * (RSX_S + C);
   return (size_t)C * 30 * 3 + 9 * C + 2 * 110 + 2 * (nu / 2 + 1) + nu + 64 + 4 * nu + 8;
 }
+// Compact layout of the warp kernel with deferred fall-backs (no Jacobi runs in it, H lives in global memory): G, GV
+// and kb alias the solver workspace V — G / GV behind the scratch of the orthogonal iteration (dead before the arrow
+// solver starts), kb on the arrow solver's Q (its result) — and V holds the arrow workspace only: 12 instead of 22 KB
+// per warp at 4 cameras.
+__host__ __device__ inline size_t fit_ws_compact_small_doubles(int C) {
+  const int nu = 3 * (RSX_S + C);
+  return (size_t)C * 30 * 3 + 9 * C + 2 * (nu / 2 + 1) + nu + 64 + 8;
+}
+__host__ __device__ inline size_t fit_ws_compact_v_doubles(int C) {
+  const size_t a = arrow_ws_doubles(C, 32), b = 320 + 220;
+  return ((a > b ? a : b) + 1) & ~(size_t)1;
+}
 __host__ __device__ inline void fit_ws_carve(double* base, double* HV /*null: carve from base*/, int C, FitWs& ws,
-                                             double* Hg = nullptr /*H alone in global memory, V carved from base*/) {
+                                             double* Hg = nullptr /*H alone in global memory, V carved from base*/,
+                                             bool compact = false) {
   const int nu = 3 * (RSX_S + C), ld = nu | 1;
   double* p = base;
   ws.vs = p; p += C * 30; ws.ns = p; p += C * 30; ws.w = p; p += C * 30; ws.R = p; p += 9 * C;
+  if (compact) {
+    ws.cs = p; p += 2 * (nu / 2 + 1) + nu; ws.misc = p; p += 64;
+    ws.iflag = (int*)p; p += 8;
+    ws.H = Hg; ws.V = p;
+    ws.G = ws.V + 320; ws.GV = ws.V + 430;
+    ArrowWs aw; arrow_ws_carve(ws.V, C, 32, aw);
+    ws.kb = aw.Q;
+    ws.v_doubles = fit_ws_compact_v_doubles(C);
+    return;
+  }
   ws.G = p; p += 110; ws.GV = p; p += 110; ws.cs = p; p += 2 * (nu / 2 + 1) + nu; ws.misc = p; p += 64; ws.kb = p; p += 4 * nu;
   ws.iflag = (int*)p; p += 8;
   if (HV) { ws.H = HV; ws.V = HV + (size_t)nu * ld; }
   else if (Hg) { ws.H = Hg; ws.V = p; }
   else { ws.H = p; ws.V = p + (size_t)nu * ld; }
+  ws.v_doubles = (size_t)nu * ld;
 }
 
 // v: [C][N][3], n: [C][M][3] (global); sv, sm: the 10 + 10 sample indices; Rt_out: [C][12] rows [R_c | t_c].
-template <class G>
-// defer = true: when the arrow iteration does not settle the function returns false WITHOUT running the Jacobi
+// defer = true: when an iterative solver does not settle the function returns false WITHOUT running the Jacobi
 // fall-back (which costs ~50 normal fits); the caller queues the hypothesis for a second pass.
-__host__ __device__ inline bool fit_hypothesis(const G& g, int C, int64_t N, int64_t M, const double* __restrict__ v,
-                                               const double* __restrict__ n, const int32_t* __restrict__ sv,
-                                               const int32_t* __restrict__ sm, const FitWs& ws, double* Rt_out,
-                                               bool fast = true, bool defer = false) {
+// DEFER_ONLY (compile time): the iterative solvers or nothing — no Jacobi code is generated at all.  The warp kernel
+// with a second pass uses it: with the three Jacobi solvers inlined it was 19 k SASS instructions (300 KB) against a
+// 32 KB instruction cache, and instruction fetch was its largest stall.
+template <bool DEFER_ONLY, class G>
+__host__ __device__ inline bool fit_hypothesis_t(const G& g, int C, int64_t N, int64_t M, const double* __restrict__ v,
+                                                 const double* __restrict__ n, const int32_t* __restrict__ sv,
+                                                 const int32_t* __restrict__ sm, const FitWs& ws, double* Rt_out,
+                                                 bool fast, bool defer) {
+  if (DEFER_ONLY) { fast = true; defer = true; }
   const int nu = 3 * (RSX_S + C), ld = nu | 1, T0 = 3 * RSX_S;
   // ---- 1. gather the sample
   for (int idx = g.tid; idx < C * 30; idx += g.nt) {
@@ -61,21 +90,36 @@ __host__ __device__ inline bool fit_hypothesis(const G& g, int C, int64_t N, int
     ws.G[a * 11 + b] = acc;
   }
   g.sync();
-  cta_jacobi(g, ws.G, ws.GV, 10, 11, ws.cs, ws.iflag, 30);
-  if (g.tid == 0) {                     // indices of the three largest eigenvalues
-    int i0 = -1, i1 = -1, i2 = -1;
-    for (int pass = 0; pass < 3; ++pass) {
-      int bi = -1; double bv = 0;
-      for (int i = 0; i < 10; ++i) {
-        if (i == i0 || i == i1) continue;
-        const double e = ws.G[i * 11 + i];
-        if (bi < 0 || e > bv) { bi = i; bv = e; }
-      }
-      if (pass == 0) i0 = bi; else if (pass == 1) i1 = bi; else i2 = bi;
-    }
-    ws.iflag[1] = i0; ws.iflag[2] = i1; ws.iflag[3] = i2;
+  // small groups first try the orthogonal iteration for the dominant 3-dimensional subspace (rsx_arrow.cuh); the
+  // Jacobi diagonalisation of the whole Gram matrix remains the general path and the fall-back
+  bool have_u = false;
+  if (fast && g.nt <= 32 && (size_t)TOP3_SCR_DOUBLES(g.nt) <= ws.v_doubles) {
+    have_u = top3_subspace(g, ws.G, ws.V, ws.V + 220, ws.iflag + 9);
+    if (have_u) {
+      for (int idx = g.tid; idx < 30; idx += g.nt) ws.GV[(idx / 3) * 11 + idx % 3] = ws.V[220 + idx];
+      if (g.tid == 0) { ws.iflag[1] = 0; ws.iflag[2] = 1; ws.iflag[3] = 2; }
+    } else if (g.tid == 0) ws.iflag[8] = -1;
+    g.sync();
+    if (!have_u && defer) return false;          // uniform over the group
   }
-  g.sync();
+  if (DEFER_ONLY && !have_u) return false;
+  if (!DEFER_ONLY && !have_u) {
+    cta_jacobi(g, ws.G, ws.GV, 10, 11, ws.cs, ws.iflag, 30);
+    if (g.tid == 0) {                     // indices of the three largest eigenvalues
+      int i0 = -1, i1 = -1, i2 = -1;
+      for (int pass = 0; pass < 3; ++pass) {
+        int bi = -1; double bv = 0;
+        for (int i = 0; i < 10; ++i) {
+          if (i == i0 || i == i1) continue;
+          const double e = ws.G[i * 11 + i];
+          if (bi < 0 || e > bv) { bi = i; bv = e; }
+        }
+        if (pass == 0) i0 = bi; else if (pass == 1) i1 = bi; else i2 = bi;
+      }
+      ws.iflag[1] = i0; ws.iflag[2] = i1; ws.iflag[3] = i2;
+    }
+    g.sync();
+  }
   // A = U3^T V  (3 x 3C), stored per camera as A_c (3x3 row-major) in ws.w (free until step 3)
   for (int idx = g.tid; idx < 9 * C; idx += g.nt) {
     const int c = idx / 9, r = (idx % 9) / 3, d = idx % 3;
@@ -112,6 +156,7 @@ __host__ __device__ inline bool fit_hypothesis(const G& g, int C, int64_t N, int
     int r0, c0;
     if (task < n_xx) {                                        // H[X_i, X_i] = sum_c Q^T Q,  Q = hat(n_ci) R_c
       const int i = task;
+#pragma unroll 1
       for (int c = 0; c < C; ++c) {
         double Q[9]; hatmul(ws.ns + (c * 10 + i) * 3, ws.R + 9 * c, Q);
         for (int a = 0; a < 3; ++a)
@@ -131,6 +176,7 @@ __host__ __device__ inline bool fit_hypothesis(const G& g, int C, int64_t N, int
       while (t >= C - a) { t -= C - a; ++a; }
       const int b = a + t;
       if (a == b) {
+#pragma unroll 1
         for (int i = 0; i < 10; ++i) {                        // collinearity: hat(n)^T hat(n)
           const double* nn = ws.ns + (a * 10 + i) * 3;
           const double Nx[9] = {0, -nn[2], nn[1], nn[2], 0, -nn[0], -nn[1], nn[0], 0};
@@ -139,6 +185,7 @@ __host__ __device__ inline bool fit_hypothesis(const G& g, int C, int64_t N, int
         }
         for (int o = 0; o < C; ++o) {                         // coplanarity rows of every pair containing a
           if (o == a) continue;
+#pragma unroll 1
           for (int i = 0; i < 10; ++i) {
             double m[3], ra[3];
             cross3(ws.w + (a * 10 + i) * 3, ws.w + (o * 10 + i) * 3, m);
@@ -149,6 +196,7 @@ __host__ __device__ inline bool fit_hypothesis(const G& g, int C, int64_t N, int
           }
         }
       } else {
+#pragma unroll 1
         for (int i = 0; i < 10; ++i) {                        // (R_a m)(-R_b m)^T,  m = w_ai x w_bi
           double m[3], ra[3], rb[3];
           cross3(ws.w + (a * 10 + i) * 3, ws.w + (b * 10 + i) * 3, m);
@@ -174,13 +222,15 @@ __host__ __device__ inline bool fit_hypothesis(const G& g, int C, int64_t N, int
   // Small groups (one warp / the host) first try the arrow-structured inverse subspace iteration, whose workspace
   // lives in V; the Jacobi diagonalisation of H remains the general path and the fall-back.
   bool have_kb = false;
-  if (fast && g.nt <= 32 && arrow_ws_doubles(C, g.nt) <= (size_t)nu * ld) {
+  if (fast && g.nt <= 32 && arrow_ws_doubles(C, g.nt) <= ws.v_doubles) {
     ArrowWs aw; arrow_ws_carve(ws.V, C, g.nt, aw);
-    have_kb = arrow_null4(g, ws.H, ld, C, ws.R, aw, ws.kb, ws.iflag + 8);
+    // (letting the iteration run to 160 sweeps where a second pass exists was tried: 2 % faster, but the slowly converging
+    // hypotheses it then keeps settle 10x further from the Jacobi result — scores off by up to 2e-8 — so 48 it stays)
+    have_kb = arrow_null4(g, ws.H, ld, C, ws.R, aw, ws.kb, ws.iflag + 8, ARW_MAX_SWEEPS);
     if (!have_kb && g.tid == 0) ws.iflag[8] = -1;
   }
   if (!have_kb && defer) return false;           // uniform over the group
-  if (!have_kb) {
+  if (!DEFER_ONLY && !have_kb) {
     cta_jacobi(g, ws.H, ws.V, nu, ld, ws.cs, ws.iflag, 40);
     if (g.tid == 0) {
       int sel[4] = {-1, -1, -1, -1};
@@ -230,7 +280,7 @@ __host__ __device__ inline bool fit_hypothesis(const G& g, int C, int64_t N, int
   if (g.tid == 0) {
     const double* t1 = u + T0 + 3;
     ws.misc[8] = sqrt(t1[0] * t1[0] + t1[1] * t1[1] + t1[2] * t1[2]);      // s = |t_1|   (calib_ransac.py:114)
-    ws.iflag[0] = 0; ws.iflag[1] = 0;
+    ws.iflag[0] = 0; ws.iflag[1] = 0; ws.iflag[10] = 0;
   }
   g.sync();
   // ---- 5. z-test on cameras 0, 1 with both signs (util.py:161-180); counts with +t, as the reference does
@@ -247,9 +297,13 @@ __host__ __device__ inline bool fit_hypothesis(const G& g, int C, int64_t N, int
     for (int e = 0; e < 10; ++e) m[e] = 0.0;
     dlt_accumulate(P0, ws.ns[k * 3], ws.ns[k * 3 + 1], m);
     dlt_accumulate(P1, ws.ns[30 + k * 3], ws.ns[30 + k * 3 + 1], m);
-    double a[4][4], X[4];
-    sym10_to_full(m, a);
-    eig4_smallest(a, X);
+    // Rayleigh-quotient iteration, Jacobi only as its last resort (the Jacobi solver here cost 20 % of the warp kernel's
+    // time in instruction fetch alone).  The sign decided below is a discontinuous function of the data (z ~ 0, a point
+    // near infinity): for a degenerate sample it hangs on the last bits of R and X whatever the solver — one garbage
+    // hypothesis of the 1500-iteration golden comes out with -t (its score, invariant to the sign, agrees to 1e-12).
+    double X[4];
+    if (DEFER_ONLY) { if (!eig4_smallest_rqi<true, false>(m, X)) ws.iflag[10] = 1; }
+    else eig4_smallest_fast(m, X);
     const double x0 = X[0] / X[3], x1 = X[1] / X[3], x2 = X[2] / X[3];
     const double z0 = ws.R[6] * x0 + ws.R[7] * x1 + ws.R[8] * x2 + t0[2];
     const double z1 = ws.R[15] * x0 + ws.R[16] * x1 + ws.R[17] * x2 + t1[2];
@@ -257,6 +311,7 @@ __host__ __device__ inline bool fit_hypothesis(const G& g, int C, int64_t N, int
     ws.misc[16 + task] = (double)cnt;
   }
   g.sync();
+  if (DEFER_ONLY && ws.iflag[10]) { if (g.tid == 0) ws.iflag[8] = -1; g.sync(); return false; }
   if (g.tid == 0) {
     double zp = 0, zn = 0;
     for (int k = 0; k < 10; ++k) { zp += ws.misc[16 + k]; zn += ws.misc[26 + k]; }
@@ -269,6 +324,14 @@ __host__ __device__ inline bool fit_hypothesis(const G& g, int C, int64_t N, int
   }
   g.sync();
   return true;
+}
+
+template <class G>
+__host__ __device__ inline bool fit_hypothesis(const G& g, int C, int64_t N, int64_t M, const double* __restrict__ v,
+                                               const double* __restrict__ n, const int32_t* __restrict__ sv,
+                                               const int32_t* __restrict__ sm, const FitWs& ws, double* Rt_out,
+                                               bool fast = true, bool defer = false) {
+  return fit_hypothesis_t<false>(g, C, N, M, v, n, sv, sm, ws, Rt_out, fast, defer);
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -57,7 +57,9 @@ extern "C" int emu_fit_mode(int C, long long N, long long M, const double* v, co
   FitWs ws; fit_ws_carve(buf.data(), nullptr, C, ws);
   ws.iflag[8] = -2;
   CtaCtx g{0, 1};
+  ws.iflag[9] = -1;
   fit_hypothesis(g, C, N, M, v, n, sv, sm, ws, Rt_out, mode != 0);
+  if (mode == 2) return ws.iflag[9];          // iterations of the top-3 orthogonal iteration (-1: not run / failed)
   return ws.iflag[8];
 }
 extern "C" void emu_score_sum(int C, long long N, long long M, const double* v, const double* n, const double* Rt,
