@@ -32,6 +32,17 @@ class TrfState(C.Structure):
                 ("hist", (f64 * 8) * TRF_MAX_HIST)]
 
 
+class BatchArgs(C.Structure):
+    """bax_batch_args (include/bax.h)."""
+    PP = C.POINTER(C.c_void_p)
+    _fields_ = [("n_problems", C.c_int32), ("n_workers", C.c_int32), ("device", C.c_int32),
+                ("C", C.c_int32), ("N", C.c_int32), ("J", C.c_int32), ("J3", C.c_int32), ("B", C.c_int32),
+                ("K", PP), ("y2d", PP), ("s2d", PP), ("p3d", PP), ("s3d", PP), ("bones", P_i32),
+                ("lambda1", f64), ("lambda2", f64), ("R0", PP), ("t0", PP), ("rvec0", PP),
+                ("ftol", f64), ("xtol", f64), ("gtol", f64), ("max_nfev", i64),
+                ("theta_out", vp), ("info_out", vp)]
+
+
 _SIGS = {
     "bax_last_error": (C.c_char_p, []),
     "bax_version": (i32, []),
@@ -61,6 +72,7 @@ _SIGS = {
     "bax_trf_begin": (i32, [vp, C.POINTER(TrfState), vp]),
     "bax_trf_iterate": (i32, [vp, C.POINTER(TrfState), vp]),
     "bax_trf_solve": (i32, [vp, C.POINTER(TrfState), vp]),
+    "bax_batch_solve": (i32, [C.POINTER(BatchArgs)]),
     "bax_triangulate": (i32, [vp, vp, vp, vp, P_i32, vp]),
     "bax_reproject_error": (i32, [vp, vp, vp, vp, vp, vp]),
     "bax_timing_enable": (i32, [vp, i32]),

@@ -23,43 +23,67 @@ EPS = float(np.finfo(np.float64).eps)
 
 
 # ----------------------------------------------------------------------------- SO(3) on the host
+def rodrigues_batch(rvecs):
+    """(n, 3) rvecs -> (n, 3, 3): the map cv2.Rodrigues applies at reference ba.py:29, vectorised (a sweep over
+    thousands of problems converts all its cameras at once).  `rodrigues` is this function on one vector, so the
+    two agree bit for bit by construction; transcendental functions go through `math` one value at a time (NumPy's
+    SIMD cos / sin / arccos need not round like libm's)."""
+    rv = np.asarray(rvecs, dtype=np.float64).reshape(-1, 3)
+    th = np.sqrt(rv[:, 0] * rv[:, 0] + rv[:, 1] * rv[:, 1] + rv[:, 2] * rv[:, 2])
+    small = th < EPS
+    k = rv / np.where(small, 1.0, th)[:, None]
+    c = np.array([math.cos(x) for x in th]).reshape(-1)
+    s = np.array([math.sin(x) for x in th]).reshape(-1)
+    kx = np.zeros((len(rv), 3, 3))
+    kx[:, 0, 1], kx[:, 0, 2] = -k[:, 2], k[:, 1]
+    kx[:, 1, 0], kx[:, 1, 2] = k[:, 2], -k[:, 0]
+    kx[:, 2, 0], kx[:, 2, 1] = -k[:, 1], k[:, 0]
+    R = c[:, None, None] * np.eye(3)[None] + (1 - c)[:, None, None] * (k[:, :, None] * k[:, None, :]) + s[:, None, None] * kx
+    R[small] = np.eye(3)
+    return R
+
+
 def rodrigues(rvec):
     """rvec -> R, the map cv2.Rodrigues applies at reference ba.py:29."""
-    r = np.asarray(rvec, dtype=np.float64).reshape(3)
-    th = math.sqrt(float(r @ r))
-    if th < EPS:
-        return np.eye(3)
-    k = r / th
-    c, s = math.cos(th), math.sin(th)
-    kx = np.array([[0, -k[2], k[1]], [k[2], 0, -k[0]], [-k[1], k[0], 0.0]])
-    return c * np.eye(3) + (1 - c) * np.outer(k, k) + s * kx
+    return rodrigues_batch(np.asarray(rvec, dtype=np.float64).reshape(1, 3))[0]
+
+
+def _rodrigues_inv_near_pi(R, th):
+    """cv2.Rodrigues' branch for sin(theta) ~ 0 (R already on SO(3))."""
+    rx = math.sqrt(max((R[0, 0] + 1) * 0.5, 0.0))
+    ry = math.sqrt(max((R[1, 1] + 1) * 0.5, 0.0)) * (-1.0 if R[0, 1] < 0 else 1.0)
+    rz = math.sqrt(max((R[2, 2] + 1) * 0.5, 0.0)) * (-1.0 if R[0, 2] < 0 else 1.0)
+    if abs(rx) < abs(ry) and abs(rx) < abs(rz) and (R[1, 2] > 0) != (ry * rz > 0):
+        rz = -rz
+    v = np.array([rx, ry, rz])
+    return v * (th / np.linalg.norm(v))
+
+
+def rodrigues_inv_batch(Rs):
+    """(n, 3, 3) -> (n, 3) rvecs as cv2.Rodrigues does at reference ba.py:19: SVD-project on SO(3) first (the linear
+    calibration returns non-orthonormal rotations), then the log map.  `rodrigues_inv` is this
+    function on one matrix (bit-identical by construction)."""
+    Rs = np.asarray(Rs, dtype=np.float64).reshape(-1, 3, 3)
+    U, _, Vt = np.linalg.svd(Rs)
+    R = U @ Vt
+    r = np.stack([R[:, 2, 1] - R[:, 1, 2], R[:, 0, 2] - R[:, 2, 0], R[:, 1, 0] - R[:, 0, 1]], axis=1)
+    s = np.sqrt((r[:, 0] * r[:, 0] + r[:, 1] * r[:, 1] + r[:, 2] * r[:, 2]) * 0.25)
+    c = np.minimum(1.0, np.maximum(-1.0, (R[:, 0, 0] + R[:, 1, 1] + R[:, 2, 2] - 1) * 0.5))
+    th = np.array([math.acos(x) for x in c]).reshape(-1)
+    near = s < 1e-5
+    out = r * (0.5 * th / np.where(near, 1.0, s))[:, None]
+    for i in np.nonzero(near)[0]:
+        out[i] = np.zeros(3) if c[i] > 0 else _rodrigues_inv_near_pi(R[i], th[i])
+    return out
 
 
 def rodrigues_inv(R):
-    """R -> rvec as cv2.Rodrigues does at reference ba.py:19: SVD-project on SO(3) first (the linear
-    calibration returns non-orthonormal rotations), then the log map."""
-    U, _, Vt = np.linalg.svd(np.asarray(R, dtype=np.float64))
-    R = U @ Vt
-    r = np.array([R[2, 1] - R[1, 2], R[0, 2] - R[2, 0], R[1, 0] - R[0, 1]])
-    s = math.sqrt(float(r @ r) * 0.25)
-    c = min(1.0, max(-1.0, (np.trace(R) - 1) * 0.5))
-    th = math.acos(c)
-    if s < 1e-5:
-        if c > 0:
-            return np.zeros(3)
-        rx = math.sqrt(max((R[0, 0] + 1) * 0.5, 0.0))
-        ry = math.sqrt(max((R[1, 1] + 1) * 0.5, 0.0)) * (-1.0 if R[0, 1] < 0 else 1.0)
-        rz = math.sqrt(max((R[2, 2] + 1) * 0.5, 0.0)) * (-1.0 if R[0, 2] < 0 else 1.0)
-        if abs(rx) < abs(ry) and abs(rx) < abs(rz) and (R[1, 2] > 0) != (ry * rz > 0):
-            rz = -rz
-        v = np.array([rx, ry, rz])
-        return v * (th / np.linalg.norm(v))
-    return r * (0.5 * th / s)
+    return rodrigues_inv_batch(np.asarray(R, dtype=np.float64).reshape(1, 3, 3))[0]
 
 
 def to_theta(R, t, x):
     """reference ba.py:18-20."""
-    rv = np.concatenate([rodrigues_inv(Rc) for Rc in R])
+    rv = rodrigues_inv_batch(R).reshape(-1)
     return np.concatenate([rv, np.asarray(t, dtype=np.float64).reshape(-1),
                            np.asarray(x, dtype=np.float64).reshape(-1)])
 
@@ -68,8 +92,7 @@ def from_theta(theta, C):
     """reference ba.py:23-31."""
     theta = np.asarray(theta, dtype=np.float64)
     rv = theta[:3 * C].reshape(C, 3)
-    return (np.stack([rodrigues(r) for r in rv]), theta[3 * C:6 * C].reshape(C, 3, 1),
-            theta[6 * C:].reshape(-1, 3))
+    return (rodrigues_batch(rv), theta[3 * C:6 * C].reshape(C, 3, 1), theta[6 * C:].reshape(-1, 3))
 
 
 # ----------------------------------------------------------------------------- device problem
@@ -745,6 +768,83 @@ def _worker_stream(dev, i):
     return pool[i]
 
 
+def _ba_batch_native(idx, problems, lambda1, lambda2, n_workers, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None,
+                     return_info=False):
+    """The sweep behind ONE C call per problem shape (bax_batch_solve, csrc/bax_batch.cu): native worker threads, each
+    with its own stream and libbax handle, run per problem the very sequence ba_main runs.  The interpreter only
+    prepares pointers and converts all rotations at once (rodrigues_inv_batch / rodrigues_batch) — per-problem Python
+    under the GIL (~1 ms) was what capped the threaded sweep at ~800 problems/s.  -> {index: result}."""
+    L = lib()
+    dev = torch.cuda.current_device()
+    f8 = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+    groups = {}
+    for k in idx:
+        p = problems[k]
+        ss2d = np.asarray(p[5])
+        has3 = p[6] is not None and p[7] is not None
+        key = (len(p[0]),) + tuple(ss2d.shape) + ((np.asarray(p[7]).shape[2],) if has3 else (0,))
+        groups.setdefault(key, []).append(k)
+    out = {}
+    bones = np.ascontiguousarray(OP_BONE, dtype=np.int32)
+    for (Cn, C2, N, J, J3), ks in groups.items():
+        assert Cn == C2
+        n = len(ks)
+        keep, cols = {}, {name: [] for name in ("K", "y", "s", "p3", "s3", "R", "t")}
+
+        def arr(a, shape):                      # one contiguous float64 copy per distinct array object
+            key = id(a)
+            if key not in keep:
+                b = f8(a).reshape(shape)
+                keep[key] = (a, b)
+            return keep[key][1]
+        Rall = np.empty((n, Cn, 3, 3))
+        for i, k in enumerate(ks):
+            camid, K, R, t, sp2d, ss2d, sp3d, ss3d = problems[k]
+            cols["K"].append(arr(K, (Cn, 3, 3))); cols["y"].append(arr(sp2d, (Cn, N * J, 2)))
+            cols["s"].append(arr(ss2d, (Cn, N * J)))
+            if J3:
+                cols["p3"].append(arr(sp3d, (Cn, N, J3, 3))); cols["s3"].append(arr(ss3d, (Cn, N, J3)))
+            cols["R"].append(arr(R, (Cn, 3, 3))); cols["t"].append(arr(t, (Cn, 3)))
+            Rall[i] = cols["R"][-1]
+        rvec = np.ascontiguousarray(rodrigues_inv_batch(Rall.reshape(-1, 3, 3)).reshape(n, Cn, 3))
+        ptrs = lambda xs: (C.c_void_p * n)(*[x.ctypes.data for x in xs])
+        npar = 6 * Cn + 3 * N * J
+        theta = np.empty((n, npar))
+        info = np.zeros((n, 8))
+        a = _lib.BatchArgs()
+        a.n_problems, a.n_workers, a.device = n, max(1, int(n_workers)), dev
+        a.C, a.N, a.J, a.J3, a.B = Cn, N, J, J3 or J, int(bones.shape[0])
+        pK, py, ps_, pR, pt = ptrs(cols["K"]), ptrs(cols["y"]), ptrs(cols["s"]), ptrs(cols["R"]), ptrs(cols["t"])
+        prv = (C.c_void_p * n)(*[rvec[i].ctypes.data for i in range(n)])
+        a.K, a.y2d, a.s2d, a.R0, a.t0, a.rvec0 = pK, py, ps_, pR, pt, prv
+        if J3:
+            p3, s3 = ptrs(cols["p3"]), ptrs(cols["s3"])
+            a.p3d, a.s3d = p3, s3
+        a.bones = bones.ctypes.data_as(_lib.P_i32)
+        a.lambda1, a.lambda2 = float(lambda1), float(lambda2)
+        a.ftol, a.xtol, a.gtol = float(ftol), float(xtol), float(gtol)
+        a.max_nfev = 0 if max_nfev is None else int(max_nfev)
+        a.theta_out, a.info_out = theta.ctypes.data, info.ctypes.data
+        check(L.bax_batch_solve(C.byref(a)), "bax_batch_solve")
+        Rs = rodrigues_batch(theta[:, :3 * Cn].reshape(-1, 3)).reshape(n, Cn, 3, 3)
+        for i, k in enumerate(ks):
+            st = int(info[i, 0])
+            if st == -10:
+                raise Exception(f"ba_batch: problem {k}: not enough constraint")          # reference util.py:320-321
+            if st == -11:
+                raise ValueError(f"ba_batch: problem {k}: Initial guess is outside of provided bounds")
+            th = theta[i]
+            R, t, x = Rs[i].copy(), th[3 * Cn:6 * Cn].reshape(Cn, 3, 1).copy(), th[6 * Cn:].reshape(-1, 3).copy()
+            if return_info:
+                res = dict(x=th.copy(), cost=info[i, 1], optimality=info[i, 6], nfev=int(info[i, 3]), njev=int(info[i, 4]),
+                           status=st, iterations=int(info[i, 5]), history=[], message=TERMINATION_MESSAGES[st],
+                           initial_cost=info[i, 2])
+                out[k] = (R, t, x, res)
+            else:
+                out[k] = (R, t, x)
+    return out
+
+
 def ba_batch(problems, lambda1, lambda2, *, n_streams=12, group=None, gather=True, solve=None, **kw):
     """Multi-sequence sweep: `ba_main` on every entry of `problems` — a sequence of
     (camid, K, R_w2c, t_w2c, sp2d, ss2d, sp3d, ss3d) tuples (or callables returning one, so a sweep need not
@@ -774,8 +874,17 @@ def ba_batch(problems, lambda1, lambda2, *, n_streams=12, group=None, gather=Tru
         kw.setdefault("verbose", False)
     results = {}
     errors = []
+    native_ok = (solve is ba_main and os.environ.get("BAX_BATCH_HOST", "0") != "1" and
+                 not any(callable(problems[k]) for k in mine) and
+                 set(kw) <= {"verbose", "ftol", "xtol", "gtol", "max_nfev", "return_info"} and not kw.get("verbose"))
+    if native_ok and mine:
+        opts = {k: v for k, v in kw.items() if k != "verbose"}
+        results = _ba_batch_native(mine, problems, lambda1, lambda2, n_streams, **opts)
+        mine_done = True
+    else:
+        mine_done = False
     q = queue.SimpleQueue()
-    for k in mine:
+    for k in ([] if mine_done else mine):
         q.put(k)
 
     def worker(i=0):
@@ -804,7 +913,9 @@ def ba_batch(problems, lambda1, lambda2, *, n_streams=12, group=None, gather=Tru
                 ctx.__exit__(None, None, None)
 
     n_thr = max(1, min(int(n_streams), len(mine)))
-    if n_thr == 1:
+    if mine_done:
+        pass
+    elif n_thr == 1:
         worker()
     else:
         dev = torch.cuda.current_device() if torch.cuda.is_available() else None

@@ -131,6 +131,34 @@ int bax_trf_begin(bax_handle* h, bax_trf_state* st, void* stream);    /* lineari
 int bax_trf_iterate(bax_handle* h, bax_trf_state* st, void* stream);  /* one pass of the outer loop body */
 int bax_trf_solve(bax_handle* h, bax_trf_state* st, void* stream);    /* after begin: iterate until termination; hist = last pass */
 
+/* ---- sweep over independent, identically shaped problems: BASELINE configs[4] (4096 four-camera scenes); the reference
+ * runs ba.py once per sequence from run_all.sh (ba.py:157-210 each).  HOST pointers throughout: per-problem arrays are
+ * given as arrays of n_problems pointers (a problem may appear more than once), shapes as for bax_problem_set.
+ * n_workers native threads, each with its own stream and handle, run per problem exactly what ba_main runs:
+ * bax_problem_set -> bax_triangulate(R0, t0) -> theta0 = [rvec0 | t0 | X] -> bax_trf_begin -> bax_trf_solve.
+ * theta_out [n_problems][6C + 3NJ]; info_out [n_problems][8] = { status (SciPy's 0..4; -10: triangulation met a
+ * rank-deficient point, -11: non-finite start), cost, initial cost, nfev, njev, iterations, optimality, tri status }.
+ * Replicas only, no collective.  Blocks until every problem is done. */
+typedef struct bax_batch_args {
+  int32_t n_problems, n_workers, device;
+  int32_t C, N, J, J3, B;
+  const double* const* K;        /* [C][9]        */
+  const double* const* y2d;      /* [C][N*J][2]   */
+  const double* const* s2d;      /* [C][N*J]      */
+  const double* const* p3d;      /* [C][N][J3][3] or NULL */
+  const double* const* s3d;      /* [C][N][J3]    or NULL */
+  const int32_t* bones;          /* [B][2]        */
+  double lambda1, lambda2;
+  const double* const* R0;       /* [C][9]  start cameras (as given to ba_main) */
+  const double* const* t0;       /* [C][3]  */
+  const double* const* rvec0;    /* [C][3]  cv2.Rodrigues(R0) (ba.py:19) */
+  double ftol, xtol, gtol;
+  int64_t max_nfev;              /* <= 0: 100 n */
+  double* theta_out;
+  double* info_out;
+} bax_batch_args;
+int bax_batch_solve(const bax_batch_args* a);
+
 /* Weighted linear triangulation of every (frame, joint) — util.triangulate_with_conf,
  * reference util.py:325-354 (+ triangulate_point 308-322).  R [C][9], t [C][3]; X [N*J][3] (NaN where
  * the reference returns NaN); status_host: 0 ok, 1 = some point has rank < 3 ("not enough constraint"). */

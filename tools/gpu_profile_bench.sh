@@ -6,7 +6,7 @@ python - <<PY
 import json
 d=json.loads(open("gpurun_out/bench_default.json").read().strip().splitlines()[-1])
 print("value %.4g e2e %.4g ms/step %.3f" % (d["value"], d["e2e"]["value"], d["ms_per_step"]), "rj", d["roofline"]["frac"], d["clocks"], d["cpu_baseline"]["value"], d["cpu_baseline"]["cores"], "ransac", d["ransac"]["value"], "launches", d["gpu_launches"])
-print(d["lm"]); print(d["batch"]["value"], d["batch"]["single_stream_problems_per_s_one_gpu"])
+print(d["lm"]); print(d["batch"]["value"], d["batch"]["single_worker_problems_per_s_one_gpu"])
 PY
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"; tail -c 400 gpurun_out/bench_ref.json
 timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/launches_bench_default.csv python bench.py --steps 4 --warmup 3 --no-cpu --batch 4 > gpurun_out/ncu_bench.log 2>&1; echo "launch list rc=$?"
