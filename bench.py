@@ -379,8 +379,8 @@ def run_gpu(args):
     comm = None
     if world > 1:      # device time inside the all-reduces (waiting for the slowest rank included), separate pass
         names = ["bone", "cost", "lin", "schur", "rhs2", "step", "norm", "gmax"]
+        prob.comm_events = []       # instrumented pass: the host-language loop with timed torch.distributed all-reduces
         sol = ba.TRFSolver(prob, theta0, ftol=0.0, xtol=0.0, gtol=0.0)
-        prob.comm_events = []
         barrier()
         ev0.record()
         for _ in range(6):
@@ -411,7 +411,10 @@ def run_gpu(args):
                            "step": "one trust-region outer iteration (SciPy trf_no_bounds body): damped Schur solves + "
                                    "cost evaluations until acceptance, then re-linearisation",
                            "cache": "inputs larger than L2 (observations + whitened blocks >> 126 MB)",
-                           "parallelism": f"frames sharded over {world} GPU(s); all-reduce of the packed camera blocks"},
+                           "parallelism": f"frames sharded over {world} GPU(s); all-reduce of the packed camera blocks",
+                           "collectives": ("NCCL issued inside libbax between the kernel phases (5 per iteration)"
+                                           if getattr(prob, "native_comm", None) is not None else
+                                           ("torch.distributed between ctypes calls" if world > 1 else "none (one GPU)"))},
                 "lm": {"cost_evaluations_per_step": nfev / args.steps, "damped_solves_per_step": trials / args.steps,
                        "cost": lm_cost, "restarts": run.restarts, "kernel_ms_2_steps": shares},
                 "e2e": {"value": e2e_value, "unit": "observations/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

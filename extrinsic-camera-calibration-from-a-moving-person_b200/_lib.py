@@ -73,6 +73,11 @@ _SIGS = {
     "bax_trf_iterate": (i32, [vp, C.POINTER(TrfState), vp]),
     "bax_trf_solve": (i32, [vp, C.POINTER(TrfState), vp]),
     "bax_batch_solve": (i32, [C.POINTER(BatchArgs)]),
+    "bax_comm_unique_id": (i32, [vp]),
+    "bax_comm_create": (i32, [i32, vp, i32, i32, C.POINTER(vp)]),
+    "bax_comm_destroy": (i32, [vp]),
+    "bax_allreduce_attach": (i32, [vp, vp]),
+    "bax_comm_stats": (i32, [vp, P_i64]),
     "bax_triangulate": (i32, [vp, vp, vp, vp, P_i32, vp]),
     "bax_reproject_error": (i32, [vp, vp, vp, vp, vp, vp]),
     "bax_timing_enable": (i32, [vp, i32]),

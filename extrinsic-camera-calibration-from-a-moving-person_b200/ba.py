@@ -108,6 +108,39 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+_native_comms = {}
+
+
+def _native_comm(group, dev):
+    """libbax's own NCCL communicator over the ranks of a torch.distributed group (one per group and device, kept for
+    the life of the process): rank 0 draws the unique id, torch.distributed hands it round, every rank joins.  The
+    trust-region driver in the library then all-reduces the packed buffers itself (bax_allreduce_attach).  Returns None
+    when NCCL cannot be bound or BAX_NATIVE_COMM=0 — the host-language all-reduces remain."""
+    import torch.distributed as dist
+    if os.environ.get("BAX_NATIVE_COMM", "1") == "0" or dist.get_backend(group) != "nccl":
+        return None
+    key = (id(group), dev.index)
+    if key not in _native_comms:
+        L = lib()
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        buf = C.create_string_buffer(128)
+        ok = 1
+        if rank == 0:
+            ok = 1 if L.bax_comm_unique_id(buf) == 0 else 0
+        box = [bytes(buf.raw) if ok else None]
+        dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0), group=group)
+        comm = C.c_void_p()
+        good = box[0] is not None and L.bax_comm_create(dev.index or 0, box[0], rank, world, C.byref(comm)) == 0
+        flag = torch.tensor([1 if good else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)            # all ranks or none
+        if int(flag.item()) == 0:
+            if good:
+                L.bax_comm_destroy(comm)
+            comm = None
+        _native_comms[key] = comm
+    return _native_comms[key]
+
+
 class BAProblem:
     """One BA problem bound to one GPU.  Arguments are what reference ba.objfun receives
     (ba.py:113): K (C,3,3), sp2d (C,N*J,2) or (C,N,J,2), ss2d (C,N,J), sp3d (C,N,J3,3), ss3d (C,N,J3).
@@ -156,6 +189,11 @@ class BAProblem:
         self.group = group
         self.comm_events = None
         self._views = {}
+        self.native_comm = None
+        if group is not None:
+            self.native_comm = _native_comm(group, self.dev)
+            if self.native_comm is not None:
+                check(self.L.bax_allreduce_attach(self.h, self.native_comm), "bax_allreduce_attach")
         if n_frames_global is not None:
             check(self.L.bax_set_global_frames(self.h, int(n_frames_global)), "bax_set_global_frames")
         self._out4 = (C.c_double * 8)()
@@ -503,11 +541,13 @@ class TRFSolver:
         # speculative: a trial point is linearised straight away (its cost falls out of the linearisation), so an
         # accepted step needs no separate cost pass; a rejected step restores the saved linearisation
         self.speculative = speculative
-        # native: the same loop behind one C-ABI call per outer iteration (csrc/bax_trf.cu) — one GPU only; a
-        # frame-sharded run all-reduces between the phases and stays in this class's Python statements
+        # native: the same loop behind one C-ABI call per outer iteration (csrc/bax_trf.cu); a frame-sharded run
+        # all-reduces between the phases inside the library too, through the communicator attached to the handle
         if native is None:
             native = os.environ.get("BAX_TRF_HOST", "0") != "1"
-        self.native = bool(native) and speculative and prob.group is None
+        # (a frame-sharded run needs libbax's own communicator for that; an instrumented pass — comm_events — stays here)
+        self.native = bool(native) and speculative and (prob.group is None or
+                                                        (prob.native_comm is not None and prob.comm_events is None))
         self.x = prob._dev_theta(theta0).clone()
         self.x_new = torch.empty_like(self.x)
         self.ftol, self.xtol, self.gtol = ftol, xtol, gtol

@@ -37,6 +37,8 @@ struct bax_handle {
   int64_t P;                 // N*J points
   double lam1, lam2;
   int64_t n_frames_global;
+  void* comm;                // ncclComm_t of a frame-sharded run (borrowed; bax_allreduce_attach) or NULL
+  int64_t n_collectives;     // collectives issued by the native driver since bax_create
   const double* K;           // [C][9]      (copied)
   const double* y2d;         // [C][P][2]   (caller-owned)
   const double* s2d;         // [C][P]      (caller-owned)
@@ -259,3 +261,5 @@ int bax_scatter_cam_step(bax_handle* h, double* step, cudaStream_t s);
 int bax_bone_pass1(bax_handle* h, const double* theta, cudaStream_t s);
 int bax_bone_pass2(bax_handle* h, const double* theta, double* out, cudaStream_t s);
 int bax_reduce_partials(bax_handle* h, const double* partials, int nblk, int nv, double* out, cudaStream_t s);
+int bax_allreduce(bax_handle* h, int which, bool op_max, cudaStream_t s);           // bax_comm.cu; no-op without a communicator
+int bax_allreduce_pair(bax_handle* h, int which_sum, int which_max, cudaStream_t s);

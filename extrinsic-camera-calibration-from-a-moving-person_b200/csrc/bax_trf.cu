@@ -1,8 +1,9 @@
 // Trust-region driver on the native side of the C ABI: the scalar logic of SciPy's trf_no_bounds
 // (scipy/optimize/_lsq/trf.py:415-587; solve_lsq_trust_region, update_tr_radius, check_termination in
 // _lsq/common.py:57-168,222-248,705-717) — the solver reference ba.py:187-206 runs — around the linearise / damped
-// Schur solve phases of this library.  One GPU, no frame sharding (a sharded run all-reduces between the phases and
-// is driven from the host language, calib_b200/ba.py TRFSolver, which this file mirrors statement by statement).
+// Schur solve phases of this library.  A frame-sharded run attaches an NCCL communicator (bax_allreduce_attach,
+// bax_comm.cu) and the packed buffers are all-reduced here, between the phases, on the compute stream; the host-language
+// twin (calib_b200/ba.py TRFSolver, which this file mirrors statement by statement) remains for instrumented passes.
 // What it buys: a whole outer iteration — or a whole solve — is ONE call across the ABI, so a sweep over many small
 // problems (BASELINE configs[4]) runs its worker streams without the host interpreter between the kernels.
 #include "bax_internal.cuh"
@@ -19,9 +20,13 @@ struct Lin { double cost, g_inf, g_2, x_norm, h_scale; };
 
 int linearize(bax_handle* h, const double* theta, Lin& o, cudaStream_t s) {
   int rc;
+  // frame-sharded runs: the packed buffers are summed over the ranks between the phases (no-ops without a communicator)
   if ((rc = bax_linearize_begin(h, theta, s))) return rc;
+  if ((rc = bax_allreduce(h, BAX_BUF_BONE, false, s))) return rc;
   if ((rc = bax_linearize_mid(h, s))) return rc;
+  if ((rc = bax_allreduce(h, BAX_BUF_LIN, false, s))) return rc;
   if ((rc = bax_linearize_post(h, s))) return rc;
+  if ((rc = bax_allreduce_pair(h, BAX_BUF_NORM, BAX_BUF_GMAX, s))) return rc;
   double out[8];
   if ((rc = bax_linearize_finish(h, out, s))) return rc;
   o.cost = out[0]; o.g_inf = out[1]; o.g_2 = out[2]; o.x_norm = out[3]; o.h_scale = out[4];
@@ -33,7 +38,9 @@ int trial(bax_handle* h, bax_trf_state* st, double alpha, int need_phi, double o
   int rc;
   st->n_trials += 1;
   if ((rc = bax_trial_begin(h, alpha, s))) return rc;
+  if ((rc = bax_allreduce(h, BAX_BUF_SCHUR, false, s))) return rc;
   if ((rc = bax_trial_mid(h, st->step, need_phi, s))) return rc;
+  if ((rc = bax_allreduce(h, BAX_BUF_RHS2, false, s))) return rc;
   if ((rc = bax_trial_finish(h, out, s))) return rc;
   if (!(isfinite(out[0]) && isfinite(out[1]))) {
     bax_set_error("non-finite trial step at alpha=%g: reduced camera system not SPD", alpha);
@@ -71,6 +78,7 @@ int solve_tr(bax_handle* h, bax_trf_state* st, double Delta, double g_norm2, dou
     if (phi < 0 && alpha <= alpha_floor) { r = {alpha, it + 1, p_norm, o[1], false}; return BAX_OK; }
     if (lazy) {
       if ((rc = bax_trial_phi_prime(h, s))) return rc;
+      if ((rc = bax_allreduce(h, BAX_BUF_RHS2_HEAD, false, s))) return rc;
       if ((rc = bax_trial_finish(h, o, s))) return rc;
     }
     if (!(o[2] > 0 && p_norm > 0)) break;

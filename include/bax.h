@@ -131,6 +131,21 @@ int bax_trf_begin(bax_handle* h, bax_trf_state* st, void* stream);    /* lineari
 int bax_trf_iterate(bax_handle* h, bax_trf_state* st, void* stream);  /* one pass of the outer loop body */
 int bax_trf_solve(bax_handle* h, bax_trf_state* st, void* stream);    /* after begin: iterate until termination; hist = last pass */
 
+/* ---- collectives inside the library (frame-sharded runs).  With a communicator attached, bax_trf_begin /
+ * _iterate / _solve all-reduce the packed buffers themselves between their phases, on the call's stream: BONE -> LIN ->
+ * {NORM (sum), GMAX (max)} in one group call per linearisation, SCHUR -> RHS2 per damped solve (5 collectives per
+ * trust-region iteration, none of them through the host language).  NCCL is bound at run time (dlopen of libnccl.so.2);
+ * no reference counterpart (the reference is single-process).
+ *   bax_comm_unique_id : HOST, rank 0: 128 bytes to be handed to every rank (ncclGetUniqueId)
+ *   bax_comm_create    : every rank, collectively (ncclCommInitRank); the communicator can serve many handles
+ *   bax_allreduce_attach(h, comm) : comm is an ncclComm_t (this library's or the caller's own); NULL detaches
+ *   bax_comm_stats     : out_host[0..1] = { attached, collectives issued since bax_create } */
+int bax_comm_unique_id(void* id128_host);
+int bax_comm_create(int device, const void* id128_host, int rank, int world, void** comm_out);
+int bax_comm_destroy(void* comm);
+int bax_allreduce_attach(bax_handle* h, void* nccl_comm);
+int bax_comm_stats(bax_handle* h, int64_t* out_host);
+
 /* ---- sweep over independent, identically shaped problems: BASELINE configs[4] (4096 four-camera scenes); the reference
  * runs ba.py once per sequence from run_all.sh (ba.py:157-210 each).  HOST pointers throughout: per-problem arrays are
  * given as arrays of n_problems pointers (a problem may appear more than once), shapes as for bax_problem_set.

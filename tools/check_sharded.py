@@ -12,7 +12,11 @@ import json
 import os
 import sys
 
+import ctypes
+
 import numpy as np
+
+C_int64 = ctypes.c_int64
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch  # noqa: E402
@@ -65,12 +69,31 @@ def main():
     worst = max(worst, out["step_cam_rel"], out["step_pts_rel"])
     # complete solves
     s_full = ba.TRFSolver(full, th_full, ftol=1e-10, xtol=1e-12, gtol=1e-12, max_nfev=30, native=False)
-    s_shard = ba.TRFSolver(shard, th_loc, ftol=1e-10, xtol=1e-12, gtol=1e-12, max_nfev=30)
+    s_shard = ba.TRFSolver(shard, th_loc, ftol=1e-10, xtol=1e-12, gtol=1e-12, max_nfev=30, native=False)
     assert not s_shard.native
     while not s_full.done():
         s_full.iterate()
     while not s_shard.done():
         s_shard.iterate()
+    # the same sharded solve through the NATIVE driver: collectives issued inside libbax (bax_allreduce_attach), one C
+    # call per outer iteration — must walk the very same path as the host-language loop above (same statements, same
+    # collectives in the same order: NCCL sums are deterministic for a fixed communicator)
+    out["native_comm"] = shard.native_comm is not None
+    if shard.native_comm is not None:
+        s_nat = ba.TRFSolver(shard, th_loc, ftol=1e-10, xtol=1e-12, gtol=1e-12, max_nfev=30)
+        assert s_nat.native
+        while not s_nat.done():
+            s_nat.iterate()
+        hn = s_nat.history
+        out["native_nfev"] = s_nat.nfev
+        out["native_vs_host_cost_rel"] = rel(s_nat.cost, s_shard.cost)
+        out["native_vs_host_x_abs"] = float(torch.max(torch.abs(s_nat.x - s_shard.x)).item())
+        out["native_vs_host_history_rel"] = max([rel(a["cost_new"], b["cost_new"]) for a, b in zip(hn, s_shard.history)] + [0.0])
+        st = (C_int64 * 2)()
+        shard.L.bax_comm_stats(shard.h, st)
+        out["native_collectives"] = int(st[1])
+        worst = max(worst, out["native_vs_host_cost_rel"], out["native_vs_host_history_rel"],
+                    0.0 if s_nat.nfev == s_shard.nfev else 1.0)
     out["nfev"] = [s_full.nfev, s_shard.nfev]
     hf, hs = s_full.history, s_shard.history
     out["history_len"] = [len(hf), len(hs)]
