@@ -85,6 +85,36 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Best effort: run this rank on the CPUs of the NUMA node its GPU hangs off BEFORE the pinned observation buffers
+    are allocated, so that first touch puts them in node-local DRAM (8 ranks x 331 MB of upload per step otherwise cross
+    the socket interconnect: VERDICT r01, e2e at 4 / 8 GPUs).  Returns a short description for the bench line."""
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(local_rank).pci_bus_id if hasattr(torch.cuda.get_device_properties(local_rank), "pci_bus_id") else None
+        if bus is None:
+            out = subprocess.run(["nvidia-smi", "--query-gpu=pci.bus_id", "--format=csv,noheader", "-i", str(local_rank)],
+                                 capture_output=True, text=True, timeout=10).stdout.strip()
+            bus = out.splitlines()[0].strip()
+        bus = bus.lower()
+        if bus.count(":") == 2 and len(bus.split(":")[0]) == 8:
+            bus = bus[4:]                                  # 00000000:1B:00.0 -> 0000:1b:00.0
+        node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read().strip())
+        if node < 0:
+            return "numa: single node / unknown"
+        cpus = []
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.extend(range(int(a), int(b or a) + 1))
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if not allowed:
+            return f"numa: node {node} has no allowed CPU"
+        os.sched_setaffinity(0, allowed)
+        return f"numa: rank bound to node {node} ({len(allowed)} CPUs)"
+    except Exception as e:          # no sysfs / no permission: leave the affinity alone
+        return f"numa: not bound ({type(e).__name__})"
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(p):
@@ -202,6 +232,7 @@ def run_gpu(args):
         dist.init_process_group("nccl", device_id=dev)
         group = dist.group.WORLD
 
+    numa = bind_to_gpu_numa_node(local_rank) if world > 1 else "numa: one GPU, not bound"
     sc, (sp2d, ss2d, sp3d, ss3d), w = make_workload(args.workload, 1000 + rank)
     C, N, J = ss2d.shape
     lam1, lam2 = w["lam"]
@@ -419,6 +450,7 @@ def run_gpu(args):
                        "cost": lm_cost, "restarts": run.restarts, "kernel_ms_2_steps": shares},
                 "e2e": {"value": e2e_value, "unit": "observations/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "steps": k_e2e, "ms_per_step": t_e2e / k_e2e * 1e3,
+                        "h2d_gb_per_s_per_gpu": h2d / (t_e2e / k_e2e) / 1e9, "host_placement": numa,
                         "note": "every step: pinned-host observations + theta -> device, one full LM iteration "
                                 "(linearise, solves, cost evaluations), theta -> host; same solve-restart rule as value; the upload of step "
                                 "k+1 (second device buffer, copy stream) overlaps the kernels of step k"},

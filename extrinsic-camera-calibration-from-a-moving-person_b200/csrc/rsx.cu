@@ -26,8 +26,12 @@ k_rsx_fit(int C, int64_t N, int64_t M, const double* __restrict__ v, const doubl
 // steps, so FITW_WARPS hypotheses share a CTA, each with its own shared-memory workspace, and __syncwarp replaces the
 // CTA barrier.  A hypothesis whose iteration does not settle is finished by the same warp with the Jacobi solver.
 #define FITW_WARPS 2
-template <bool DEFER_ONLY>
-__global__ void __launch_bounds__(32 * FITW_WARPS, 8)
+// WARPS hypotheses per CTA.  LOCKSTEP: the CTA takes WARPS consecutive hypotheses at a time and meets at a barrier after
+// each batch, so that the warps of an SM walk through the same phase of the (large) code together: fewer
+// instruction-fetch stalls than the free-running version, at the price of waiting for the batch's slowest fit
+// (default where the compact layout fits 16 warps; env RSX_FIT_LOCKSTEP=0 gives the free-running kernel).
+template <bool DEFER_ONLY, int WARPS, bool LOCKSTEP>
+__global__ void __launch_bounds__(32 * WARPS, LOCKSTEP ? 1 : 16 / WARPS)
 k_rsx_fit_warp(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
                const int32_t* __restrict__ samp_v, const int32_t* __restrict__ samp_m, int64_t H,
                double* __restrict__ Rt, unsigned long long* __restrict__ stats /*[4]: fall-backs, sweeps, work counter, deferred*/,
@@ -44,23 +48,35 @@ k_rsx_fit_warp(int C, int64_t N, int64_t M, const double* __restrict__ v, const 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   FitWs ws;
   fit_ws_carve(sm + warp * per_warp, nullptr, C, ws,
-               h_global ? h_global + ((size_t)blockIdx.x * FITW_WARPS + warp) * (size_t)nu * ld : nullptr, compact != 0);
+               h_global ? h_global + ((size_t)blockIdx.x * WARPS + warp) * (size_t)nu * ld : nullptr, compact != 0);
   WarpCtx g{lane, 32};
+  __shared__ long long s_base;
   // hypotheses are handed out one at a time from a global counter: a fit's cost varies (sweep count, the rare Jacobi
   // fall-back is ~50x a normal fit), so a fixed stride leaves most SMs idle while the slowest warp finishes
   for (;;) {
     long long h = 0;
-    if (lane == 0) h = (long long)atomicAdd(stats + 2, 1ULL);
-    h = __shfl_sync(0xffffffffu, h, 0);
-    if (h >= H) break;
-    const bool done = fit_hypothesis_t<DEFER_ONLY>(g, C, N, M, v, n, samp_v + h * RSX_S, samp_m + h * RSX_S, ws,
-                                                   Rt + (size_t)h * C * 12, true, deferred != nullptr);
-    if (lane == 0) {
-      const int sw = ws.iflag[8];
-      if (sw < 0) atomicAdd(stats, 1ULL); else atomicAdd(stats + 1, (unsigned long long)sw);
-      if (!done) deferred[atomicAdd(stats + 3, 1ULL)] = (int32_t)h;     // second pass: k_rsx_fit_deferred
+    if (LOCKSTEP) {
+      if (threadIdx.x == 0) s_base = (long long)atomicAdd(stats + 2, (unsigned long long)WARPS);
+      __syncthreads();
+      const long long base = s_base;
+      if (base >= H) break;                                   // uniform over the CTA
+      h = base + warp;
+    } else {
+      if (lane == 0) h = (long long)atomicAdd(stats + 2, 1ULL);
+      h = __shfl_sync(0xffffffffu, h, 0);
+      if (h >= H) break;
+    }
+    if (h < H) {
+      const bool done = fit_hypothesis_t<DEFER_ONLY>(g, C, N, M, v, n, samp_v + h * RSX_S, samp_m + h * RSX_S, ws,
+                                                     Rt + (size_t)h * C * 12, true, deferred != nullptr);
+      if (lane == 0) {
+        const int sw = ws.iflag[8];
+        if (sw < 0) atomicAdd(stats, 1ULL); else atomicAdd(stats + 1, (unsigned long long)sw);
+        if (!done) deferred[atomicAdd(stats + 3, 1ULL)] = (int32_t)h;     // second pass: k_rsx_fit_deferred
+      }
     }
     __syncwarp();
+    if (LOCKSTEP) __syncthreads();
   }
 }
 
@@ -91,17 +107,19 @@ template <int MODE, int MINB>
 __global__ void __launch_bounds__(SCORE_THREADS, MINB)
 k_rsx_score(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
             const double* __restrict__ Rt, int64_t H, double* __restrict__ score, double* __restrict__ parts) {
-  extern __shared__ __align__(16) double sm[];       // [C][12] model, then 2*32 reduction scratch
+  extern __shared__ __align__(16) double sm[];       // [C][12] model, 2*32 reduction scratch, [C][9] R_0 R_c^T
   double* sRt = sm;
   double* red = sm + ((12 * C + 1) & ~1);
+  double* sG = red + 64;
   CtaCtx g{(int)threadIdx.x, (int)blockDim.x};
   for (int64_t h = blockIdx.x; h < H; h += gridDim.x) {
     __syncthreads();
     for (int i = threadIdx.x; i < 12 * C; i += blockDim.x) sRt[i] = Rt[(size_t)h * C * 12 + i];
     __syncthreads();
     double acc[2];
+    if (MODE == 1) { score_dirs_prepare(g, C, sRt, sG); __syncthreads(); }
     acc[0] = score_points_sum<MODE>(g, C, M, n, sRt);
-    acc[1] = score_dirs(g, C, N, v, sRt, nullptr, 0.0, nullptr);
+    acc[1] = MODE == 1 ? score_dirs_sum(g, C, N, v, sG) : score_dirs(g, C, N, v, sRt, nullptr, 0.0, nullptr);
     block_sum<2>(acc, red);
     if (threadIdx.x == 0) {
       score[h] = sqrt(acc[0]) / (double)M + sqrt(acc[1]) / (double)N;      // calib_ransac.py:179-181
@@ -261,15 +279,19 @@ int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, 
     const bool compact = hglob && defer_ok && h->fit_mode != 5;   // env RSX_FIT_MODE=5: round-1 shared-memory layout
     const size_t per_warp = (compact ? ((fit_ws_compact_small_doubles(C) + fit_ws_compact_v_doubles(C) + 1) & ~(size_t)1)
                                      : ((fit_ws_small_doubles(C) + (hglob ? 1 : 2) * (size_t)nu * ld + 1) & ~(size_t)1)) * sizeof(double);
-    const size_t smem = per_warp * FITW_WARPS;
-    if (h->fit_mode != 0 && smem <= 110 * 1024 && arrow_ws_doubles(C, 32) <= (size_t)nu * ld) {
+    static const int env_warps = getenv("RSX_FIT_WARPS") ? atoi(getenv("RSX_FIT_WARPS")) : FITW_WARPS;
+    static const int env_lock = getenv("RSX_FIT_LOCKSTEP") ? atoi(getenv("RSX_FIT_LOCKSTEP")) : 1;   // default: lock-step batches (17.1 against 18.2 ms per 100 k)
+    const bool lockstep = env_lock != 0 && compact && per_warp * 16 <= 226 * 1024;
+    const int fw = lockstep ? 16 : (env_warps == 4 ? 4 : FITW_WARPS);
+    const size_t smem = per_warp * fw;
+    if (h->fit_mode != 0 && (smem <= 110 * 1024 || lockstep) && arrow_ws_doubles(C, 32) <= (size_t)nu * ld) {
       const int per_sm = (int)((226 * 1024) / (smem + 1024));       // 1 KB per resident CTA is reserved by the system
-      int64_t grid = (H + FITW_WARPS - 1) / FITW_WARPS;
+      int64_t grid = (H + fw - 1) / fw;
       const int64_t cap = (int64_t)h->sm_count * per_sm;          // resident CTAs only: work is handed out dynamically
       if (grid > cap) grid = cap;
       double* hg = nullptr;
       if (hglob) {
-        const size_t need = sizeof(double) * (size_t)nu * ld * FITW_WARPS * (size_t)cap;
+        const size_t need = sizeof(double) * (size_t)nu * ld * fw * (size_t)cap;
         if (need > h->fit_scratch_bytes) {
           if (h->fit_scratch) cudaFree(h->fit_scratch);
           h->fit_scratch = nullptr; h->fit_scratch_bytes = 0;
@@ -279,8 +301,10 @@ int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, 
         hg = h->fit_scratch;
       }
       BAX_CUDA(cudaMemsetAsync((unsigned long long*)h->fit_stats + 2, 0, 2 * sizeof(unsigned long long), s));
-      BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_warp<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_warp<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_warp<true, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_warp<true, 4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_warp<true, 16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_warp<false, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       int32_t* deferred = nullptr;
       if (h->fit_mode != 2 && small + hv <= 200 * 1024) {          // env RSX_FIT_MODE=2: fall-backs inline, as before
         if (H > h->cap_deferred) {
@@ -292,12 +316,15 @@ int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, 
         deferred = h->deferred;
       }
       RsxTimer t(h, RSX_T_FIT, s, deferred ? 2 : 1);
-      if (deferred)
-        k_rsx_fit_warp<true><<<(unsigned)grid, 32 * FITW_WARPS, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt,
-                                                                         (unsigned long long*)h->fit_stats, deferred, hg, compact ? 1 : 0);
+      unsigned long long* fst = (unsigned long long*)h->fit_stats;
+      if (deferred && lockstep)
+        k_rsx_fit_warp<true, 16, true><<<(unsigned)grid, 32 * 16, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt, fst, deferred, hg, 1);
+      else if (deferred && fw == 4)
+        k_rsx_fit_warp<true, 4, false><<<(unsigned)grid, 32 * 4, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt, fst, deferred, hg, compact ? 1 : 0);
+      else if (deferred)
+        k_rsx_fit_warp<true, 2, false><<<(unsigned)grid, 32 * 2, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt, fst, deferred, hg, compact ? 1 : 0);
       else
-        k_rsx_fit_warp<false><<<(unsigned)grid, 32 * FITW_WARPS, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt,
-                                                                          (unsigned long long*)h->fit_stats, deferred, hg, 0);
+        k_rsx_fit_warp<false, 2, false><<<(unsigned)grid, 32 * 2, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt, fst, deferred, hg, 0);
       BAX_LAUNCH_CHECK();
       if (deferred) {
         BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_deferred, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(small + hv)));
@@ -341,7 +368,7 @@ extern "C" int rsx_fit_score(rsx_handle* h, const int32_t* samp_v, const int32_t
   if (!models) { int rc = ensure_models(h, H); if (rc) return rc; models = h->Rt; }
   int rc = rsx_launch_fit(h, samp_v, samp_m, H, models, s); if (rc) return rc;
   {
-    const size_t smem = sizeof(double) * (((12 * h->C + 1) & ~1) + 2 * 32);
+    const size_t smem = sizeof(double) * (((12 * h->C + 1) & ~1) + 2 * 32 + 9 * h->C);
     int64_t grid = H < 64 * (int64_t)h->sm_count ? H : 64 * (int64_t)h->sm_count;
     RsxTimer t(h, RSX_T_SCORE, s, 1);
     if (h->score_mode == 0)

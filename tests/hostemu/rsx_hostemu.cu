@@ -66,7 +66,9 @@ extern "C" void emu_score_sum(int C, long long N, long long M, const double* v, 
                               double* parts2, int mode) {
   CtaCtx g{0, 1};
   parts2[0] = mode ? score_points_sum<1>(g, C, M, n, Rt) : score_points_sum<0>(g, C, M, n, Rt);
-  parts2[1] = score_dirs(g, C, N, v, Rt, nullptr, 0.0, nullptr);
+  std::vector<double> Gc(9 * C);
+  score_dirs_prepare(g, C, Rt, Gc.data());
+  parts2[1] = mode ? score_dirs_sum(g, C, N, v, Gc.data()) : score_dirs(g, C, N, v, Rt, nullptr, 0.0, nullptr);
 }
 extern "C" void emu_score(int C, long long N, long long M, const double* v, const double* n, const double* Rt,
                           double* parts2, double* e_out, double* e3d_out, const double* K00, double th2d, double th3d,
