@@ -232,12 +232,14 @@ def run_gpu(args):
         dist.init_process_group("nccl", device_id=dev)
         group = dist.group.WORLD
 
-    numa = bind_to_gpu_numa_node(local_rank) if world > 1 else "numa: one GPU, not bound"
     sc, (sp2d, ss2d, sp3d, ss3d), w = make_workload(args.workload, 1000 + rank)
     C, N, J = ss2d.shape
     lam1, lam2 = w["lam"]
-    y_h = torch.from_numpy(sp2d.reshape(C, N * J, 2)).pin_memory()
+    cpus0 = os.sched_getaffinity(0)
+    numa = bind_to_gpu_numa_node(local_rank) if world > 1 else "numa: one GPU, not bound"
+    y_h = torch.from_numpy(sp2d.reshape(C, N * J, 2)).pin_memory()     # first touch on the GPU's NUMA node
     s_h = torch.from_numpy(ss2d.reshape(C, N * J)).pin_memory()
+    os.sched_setaffinity(0, cpus0)                                     # the worker threads of the later legs roam again
     prob = ba.BAProblem(sc.K, y_h, s_h.reshape(C, N, J), sp3d, ss3d, ba.OP_BONE, lam1, lam2, device=dev,
                         group=group, n_frames_global=N * world)
     x0 = prob.triangulate(sc.R_init, sc.t_init)

@@ -40,7 +40,7 @@ class BatchArgs(C.Structure):
                 ("K", PP), ("y2d", PP), ("s2d", PP), ("p3d", PP), ("s3d", PP), ("bones", P_i32),
                 ("lambda1", f64), ("lambda2", f64), ("R0", PP), ("t0", PP), ("rvec0", PP),
                 ("ftol", f64), ("xtol", f64), ("gtol", f64), ("max_nfev", i64),
-                ("theta_out", vp), ("info_out", vp)]
+                ("theta_out", vp), ("info_out", vp), ("blocking_sync", C.c_int32)]
 
 
 _SIGS = {
@@ -48,6 +48,7 @@ _SIGS = {
     "bax_version": (i32, []),
     "bax_create": (i32, [i32, C.POINTER(vp)]),
     "bax_destroy": (i32, [vp]),
+    "bax_set_blocking_sync": (i32, [vp, i32]),
     "bax_problem_set": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, P_i32, f64, f64, vp]),
     "bax_problem_dims": (i32, [vp, P_i64]),
     "bax_observations_rebind": (i32, [vp, vp, vp]),

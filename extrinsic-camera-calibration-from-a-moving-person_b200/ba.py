@@ -852,7 +852,18 @@ def _ba_batch_native(idx, problems, lambda1, lambda2, n_workers, ftol=1e-4, xtol
         theta = np.empty((n, npar))
         info = np.zeros((n, 8))
         a = _lib.BatchArgs()
-        a.n_problems, a.n_workers, a.device = n, max(1, int(n_workers)), dev
+        # worker threads spin on their scalar read-backs: give every one a core.  With several ranks on one host
+        # (LOCAL_WORLD_SIZE) the cores are shared: 4 ranks x 12 workers on a 24-core box ran at a third of the single-rank
+        # rate.  Fewer workers first; sleeping waits only if even two workers per rank oversubscribe the host.
+        try:
+            cpus = len(os.sched_getaffinity(0))
+        except AttributeError:
+            cpus = os.cpu_count() or 1
+        local_world = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
+        fair = max(2, cpus // local_world - 1)
+        nw = max(1, min(int(n_workers), fair))
+        a.blocking_sync = 1 if nw * local_world > cpus else 0
+        a.n_problems, a.n_workers, a.device = n, nw, dev
         a.C, a.N, a.J, a.J3, a.B = Cn, N, J, J3 or J, int(bones.shape[0])
         pK, py, ps_, pR, pt = ptrs(cols["K"]), ptrs(cols["y"]), ptrs(cols["s"]), ptrs(cols["R"]), ptrs(cols["t"])
         prv = (C.c_void_p * n)(*[rvec[i].ctypes.data for i in range(n)])

@@ -58,6 +58,9 @@ extern "C" int bax_batch_solve(const bax_batch_args* a) {
   std::vector<Worker> W(nw);
   std::atomic<int> next(0);
   std::atomic<int> failed(0);
+  // spinning host waits are the faster ones as long as every worker thread has a core; the caller asks for sleeping
+  // waits when it has to oversubscribe the host
+  const bool block = a->blocking_sync != 0;
   const bool prof = getenv("BAX_BATCH_PROFILE") != nullptr;       // per-phase host wall time, summed over workers
   std::atomic<long long> t_ns[6];
   for (auto& t : t_ns) t.store(0);
@@ -82,6 +85,7 @@ extern "C" int bax_batch_solve(const bax_batch_args* a) {
     if (!ok) { w.rc = BAX_E_CUDA; w.err = "bax_batch_solve: worker allocation failed"; failed.store(1); return; }
     int rc = bax_create(a->device, &w.h);
     if (rc) { fail(rc, "bax_create"); return; }
+    if (block) bax_set_blocking_sync(w.h, 1);
     for (;;) {
       if (failed.load()) return;
       const int k = next.fetch_add(1);
@@ -133,7 +137,7 @@ extern "C" int bax_batch_solve(const bax_batch_args* a) {
       if (rc) { fail(rc, "bax_trf_solve"); return; }
       auto T5 = now();
       if (cudaMemcpyAsync(w.pin, st.x, sizeof(double) * n, cudaMemcpyDeviceToHost, w.s) != cudaSuccess ||
-          cudaStreamSynchronize(w.s) != cudaSuccess) { w.rc = BAX_E_CUDA; w.err = "download"; failed.store(1); return; }
+          bax_stream_wait(w.h, w.s) != cudaSuccess) { w.rc = BAX_E_CUDA; w.err = "download"; failed.store(1); return; }
       memcpy(a->theta_out + (size_t)k * n, w.pin, sizeof(double) * n);
       info[0] = (double)st.status; info[1] = st.cost; info[2] = st.initial_cost; info[3] = (double)st.nfev;
       info[4] = (double)st.njev; info[5] = (double)st.iteration; info[6] = st.g_inf;

@@ -85,7 +85,7 @@ extern "C" int bax_triangulate(bax_handle* h, const double* R, const double* t, 
   BAX_LAUNCH_CHECK();
   int hs = 0;
   BAX_CUDA(cudaMemcpyAsync(&hs, st, sizeof(int), cudaMemcpyDeviceToHost, s));
-  BAX_CUDA(cudaStreamSynchronize(s));
+  BAX_CUDA(bax_stream_wait(h, s));
   if (status_host) *status_host = hs;
   return BAX_OK;
 }

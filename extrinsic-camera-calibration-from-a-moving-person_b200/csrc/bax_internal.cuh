@@ -37,6 +37,8 @@ struct bax_handle {
   int64_t P;                 // N*J points
   double lam1, lam2;
   int64_t n_frames_global;
+  int blocking_sync;         // host waits sleep on an event instead of spinning (sweeps with many worker threads)
+  cudaEvent_t ev_block;
   void* comm;                // ncclComm_t of a frame-sharded run (borrowed; bax_allreduce_attach) or NULL
   int64_t n_collectives;     // collectives issued by the native driver since bax_create
   const double* K;           // [C][9]      (copied)
@@ -261,5 +263,12 @@ int bax_scatter_cam_step(bax_handle* h, double* step, cudaStream_t s);
 int bax_bone_pass1(bax_handle* h, const double* theta, cudaStream_t s);
 int bax_bone_pass2(bax_handle* h, const double* theta, double* out, cudaStream_t s);
 int bax_reduce_partials(bax_handle* h, const double* partials, int nblk, int nv, double* out, cudaStream_t s);
+// Host wait for the call's stream: a spinning cudaStreamSynchronize, or — bax_set_blocking_sync — a sleep on a
+// blocking-sync event, which frees the core (a sweep's 12 spinning workers per GPU starved each other: DESIGN.md §6).
+inline cudaError_t bax_stream_wait(bax_handle* h, cudaStream_t s) {
+  if (!h->blocking_sync) return cudaStreamSynchronize(s);
+  cudaError_t e = cudaEventRecord(h->ev_block, s);
+  return e != cudaSuccess ? e : cudaEventSynchronize(h->ev_block);
+}
 int bax_allreduce(bax_handle* h, int which, bool op_max, cudaStream_t s);           // bax_comm.cu; no-op without a communicator
 int bax_allreduce_pair(bax_handle* h, int which_sum, int which_max, cudaStream_t s);

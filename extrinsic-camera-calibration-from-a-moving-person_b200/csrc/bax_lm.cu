@@ -128,7 +128,7 @@ extern "C" int bax_cost_finish(bax_handle* h, double* cost_host, void* stream) {
   double* hp = h->host_pinned;
   BAX_CUDA(cudaMemcpyAsync(hp, h->buf[BAX_BUF_COST], sizeof(double) * (h->B + 2), cudaMemcpyDeviceToHost, s));
   BAX_CUDA(cudaMemcpyAsync(hp + 32, h->buf[BAX_BUF_BONE] + h->B, sizeof(double), cudaMemcpyDeviceToHost, s));
-  BAX_CUDA(cudaStreamSynchronize(s));
+  BAX_CUDA(bax_stream_wait(h, s));
   *cost_host = 0.5 * (hp[h->B] + hp[h->B + 1] + bone_cost_host(h, hp, hp[32]));
   return BAX_OK;
 }
@@ -526,7 +526,7 @@ extern "C" int bax_linearize_finish(bax_handle* h, double* out_host, void* strea
   h->t_launch[BAX_T_LIN] += 1;
   double* stage = h->host_pinned + 64;
   BAX_CUDA(cudaMemcpyAsync(stage, h->lin_stage, sizeof(double) * n_stage, cudaMemcpyDeviceToHost, s));
-  BAX_CUDA(cudaStreamSynchronize(s));
+  BAX_CUDA(bax_stream_wait(h, s));
   const double* gc = stage; const double* ssq = stage + C6;
   double ginf = stage[C6 + B + 4], g2 = stage[C6 + B + 2], x2 = stage[C6 + B + 3];
   for (int i = 0; i < C6; ++i) { ginf = fmax(ginf, fabs(gc[i])); g2 += gc[i] * gc[i]; x2 += stage[C6 + B + 8 + i] * stage[C6 + B + 8 + i]; }

@@ -145,6 +145,7 @@ extern "C" int bax_create(int device, bax_handle** out) {
   { const char* e = getenv("BAX_RJ_VARIANT"); h->rj_variant = e ? atoi(e) : -1; }
   BAX_CUDA(cudaEventCreate(&h->ev0));
   BAX_CUDA(cudaEventCreate(&h->ev1));
+  BAX_CUDA(cudaEventCreateWithFlags(&h->ev_block, cudaEventBlockingSync | cudaEventDisableTiming));
   BAX_CUDA(cudaMallocHost((void**)&h->host_pinned, (64 + 4096) * sizeof(double)));   // [0,64): trial scalars; [64,..): linearisation scalars
   {  // freed blocks stay in the device's default pool: the next handle of a sweep gets them back without a driver call
     cudaMemPool_t pool; unsigned long long keep = ~0ULL;
@@ -176,11 +177,17 @@ static void free_problem(bax_handle* h) {
   h->syrk_part_bytes = 0;
 }
 
+extern "C" int bax_set_blocking_sync(bax_handle* h, int on) {
+  if (!h) { bax_set_error("bax_set_blocking_sync: bad argument"); return BAX_E_ARG; }
+  h->blocking_sync = on ? 1 : 0;
+  return BAX_OK;
+}
+
 extern "C" int bax_destroy(bax_handle* h) {
   if (!h) return BAX_OK;
   cudaSetDevice(h->device);
   free_problem(h);
-  cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
+  cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1); cudaEventDestroy(h->ev_block);
   cudaFreeHost(h->host_pinned);
   free(h);
   return BAX_OK;
@@ -227,7 +234,7 @@ extern "C" int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B
       }
     BAX_ALLOC(h, h->joint_bones, n * sizeof(int32_t));
     BAX_CUDA(cudaMemcpyAsync(h->joint_bones, jb, n * sizeof(int32_t), cudaMemcpyHostToDevice, s));
-    BAX_CUDA(cudaStreamSynchronize(s));
+    BAX_CUDA(bax_stream_wait(h, s));
     free(jb);
   }
   // ---- orientation-term constants
@@ -247,14 +254,14 @@ extern "C" int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B
     int64_t lastp = 0; int32_t lastf = 0;
     BAX_CUDA(cudaMemcpyAsync(&lastp, pos + NB - 1, 8, cudaMemcpyDeviceToHost, s));
     BAX_CUDA(cudaMemcpyAsync(&lastf, flag + NB - 1, 4, cudaMemcpyDeviceToHost, s));
-    BAX_CUDA(cudaStreamSynchronize(s));
+    BAX_CUDA(bax_stream_wait(h, s));
     h->Nv = lastp + lastf;
     if (h->Nv > 0) {
       BAX_ALLOC(h, h->dhat, sizeof(double) * 3 * C * h->Nv);
       k_bone_dir_scatter<<<nb, 256, 0, s>>>(p3d, h->bones, flag, pos, C, N, J3, B, h->Nv, h->dhat);
       BAX_LAUNCH_CHECK();
     }
-    BAX_CUDA(cudaStreamSynchronize(s));
+    BAX_CUDA(bax_stream_wait(h, s));
     bax_dev_free(h, flag); bax_dev_free(h, f64); bax_dev_free(h, pos); bax_dev_free(h, tmp);
   }
   // ---- residual row order: exclusive scan of visible counts over (camera, 256-point block)
@@ -270,7 +277,7 @@ extern "C" int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B
     int64_t lb = 0, lc = 0;
     BAX_CUDA(cudaMemcpyAsync(&lb, h->blockbase + nb - 1, 8, cudaMemcpyDeviceToHost, s));
     BAX_CUDA(cudaMemcpyAsync(&lc, cnt + nb - 1, 8, cudaMemcpyDeviceToHost, s));
-    BAX_CUDA(cudaStreamSynchronize(s));
+    BAX_CUDA(bax_stream_wait(h, s));
     h->n_vis = lb + lc;
     bax_dev_free(h, cnt); bax_dev_free(h, tmp);
   }
@@ -304,7 +311,7 @@ extern "C" int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B
   // Yhat / Gv are allocated lazily by the first linearise (bax_lm.cu)
   h->ldy = ((3 * h->P + 31) / 32) * 32;
   h->ldv = ((h->Nv + 31) / 32) * 32;
-  BAX_CUDA(cudaStreamSynchronize(s));
+  BAX_CUDA(bax_stream_wait(h, s));
   return BAX_OK;
 }
 

@@ -243,7 +243,7 @@ extern "C" int bax_trial_finish(bax_handle* h, double* out_host, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
   int rc = bax_dense_solve2(h, s); if (rc) return rc;
   BAX_CUDA(cudaMemcpyAsync(h->host_pinned, h->buf[BAX_BUF_STEP], sizeof(double) * 4, cudaMemcpyDeviceToHost, s));
-  BAX_CUDA(cudaStreamSynchronize(s));
+  BAX_CUDA(bax_stream_wait(h, s));
   for (int i = 0; i < 4; ++i) out_host[i] = h->host_pinned[i];
   return BAX_OK;
 }

@@ -28,6 +28,9 @@ int bax_version(void);
 
 int bax_create(int device, bax_handle** out);
 int bax_destroy(bax_handle* h);
+/* Host waits of this handle's calls (scalar read-backs) sleep on a blocking-sync event instead of spinning: for callers
+ * that run many handles from many threads (bax_batch_solve does it for its workers). */
+int bax_set_blocking_sync(bax_handle* h, int on);
 
 /* Bind one BA problem (replaces the argument tuple of ba.objfun, reference ba.py:113 and
  * ba_main ba.py:157-206).  y2d [C][N*J][2], s2d [C][N*J] are referenced, not copied (caller keeps
@@ -171,6 +174,8 @@ typedef struct bax_batch_args {
   int64_t max_nfev;              /* <= 0: 100 n */
   double* theta_out;
   double* info_out;
+  int32_t blocking_sync;         /* 1: the workers' host waits sleep (bax_set_blocking_sync) instead of spinning: for
+                                    hosts with fewer cores than worker threads */
 } bax_batch_args;
 int bax_batch_solve(const bax_batch_args* a);
 
