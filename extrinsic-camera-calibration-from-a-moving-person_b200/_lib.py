@@ -74,6 +74,7 @@ _SIGS = {
     "bax_trf_iterate": (i32, [vp, C.POINTER(TrfState), vp]),
     "bax_trf_solve": (i32, [vp, C.POINTER(TrfState), vp]),
     "bax_batch_solve": (i32, [C.POINTER(BatchArgs)]),
+    "bax_batch_release": (i32, []),
     "bax_comm_unique_id": (i32, [vp]),
     "bax_comm_create": (i32, [i32, vp, i32, i32, C.POINTER(vp)]),
     "bax_comm_destroy": (i32, [vp]),

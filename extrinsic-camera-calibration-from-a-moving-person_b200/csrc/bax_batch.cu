@@ -11,6 +11,7 @@
 // are bit-identical to single ba_main calls.  Replicas only: problems share nothing, there is no collective.
 #include "bax_internal.cuh"
 #include <atomic>
+#include <mutex>
 #include <chrono>
 #include <stdlib.h>
 #include <string.h>
@@ -26,9 +27,30 @@ struct Worker {
   char* pin = nullptr;       // pinned staging: inputs of one problem, then its theta
   char* dev = nullptr;       // device mirror of the inputs
   double *x = nullptr, *x_new = nullptr, *step = nullptr, *X0 = nullptr;
+  int device = -1;
+  size_t pin_bytes = 0, dev_bytes = 0, n = 0, p3 = 0;   // capacities
   int rc = 0;
   std::string err;
 };
+
+// Workers outlive a call: creating twelve of them (pinned staging, device buffers, handle, stream) costs ~60 ms, a
+// tenth of a 512-problem sweep.  They are parked here and handed to the next call whose problems fit.
+std::mutex g_pool_mu;
+std::vector<Worker> g_pool;
+
+void worker_free(Worker& w) {
+  if (w.device >= 0) cudaSetDevice(w.device);
+  if (w.s) cudaStreamSynchronize(w.s);
+  if (w.h) bax_destroy(w.h);
+  if (w.X0) cudaFree(w.X0);
+  if (w.step) cudaFree(w.step);
+  if (w.x_new) cudaFree(w.x_new);
+  if (w.x) cudaFree(w.x);
+  if (w.dev) cudaFree(w.dev);
+  if (w.pin) cudaFreeHost(w.pin);
+  if (w.s) cudaStreamDestroy(w.s);
+  w = Worker();
+}
 
 struct Layout {              // byte offsets of one problem's inputs inside the staging block
   size_t K, y, s, p3, s3, R, t, rv, total;
@@ -56,6 +78,16 @@ extern "C" int bax_batch_solve(const bax_batch_args* a) {
   int nw = a->n_workers < 1 ? 1 : a->n_workers;
   if (nw > a->n_problems) nw = a->n_problems;
   std::vector<Worker> W(nw);
+  {  // parked workers of earlier calls that fit this problem shape
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    int got = 0;
+    for (size_t i = 0; i < g_pool.size() && got < nw;) {
+      Worker& c = g_pool[i];
+      if (c.device == a->device && c.pin_bytes >= pin_bytes && c.dev_bytes >= L.total && c.n >= (size_t)n && c.p3 >= (size_t)(3 * P)) {
+        W[got++] = c; g_pool.erase(g_pool.begin() + i);
+      } else ++i;
+    }
+  }
   std::atomic<int> next(0);
   std::atomic<int> failed(0);
   // spinning host waits are the faster ones as long as every worker thread has a core; the caller asks for sleeping
@@ -75,17 +107,22 @@ extern "C" int bax_batch_solve(const bax_batch_args* a) {
       w.rc = rc; w.err = std::string(what) + ": " + bax_last_error(); failed.store(1);
     };
     if (cudaSetDevice(a->device) != cudaSuccess) { w.rc = BAX_E_CUDA; w.err = "cudaSetDevice"; failed.store(1); return; }
-    bool ok = cudaStreamCreateWithFlags(&w.s, cudaStreamNonBlocking) == cudaSuccess &&
-              cudaHostAlloc((void**)&w.pin, pin_bytes, cudaHostAllocDefault) == cudaSuccess &&
-              cudaMalloc((void**)&w.dev, L.total) == cudaSuccess &&
-              cudaMalloc((void**)&w.x, sizeof(double) * n) == cudaSuccess &&
-              cudaMalloc((void**)&w.x_new, sizeof(double) * n) == cudaSuccess &&
-              cudaMalloc((void**)&w.step, sizeof(double) * n) == cudaSuccess &&
-              cudaMalloc((void**)&w.X0, sizeof(double) * 3 * P) == cudaSuccess;
-    if (!ok) { w.rc = BAX_E_CUDA; w.err = "bax_batch_solve: worker allocation failed"; failed.store(1); return; }
-    int rc = bax_create(a->device, &w.h);
-    if (rc) { fail(rc, "bax_create"); return; }
-    if (block) bax_set_blocking_sync(w.h, 1);
+    int rc = 0;
+    w.rc = 0; w.err.clear();
+    if (!w.h) {                                   // a fresh worker (none parked that fits)
+      bool ok = cudaStreamCreateWithFlags(&w.s, cudaStreamNonBlocking) == cudaSuccess &&
+                cudaHostAlloc((void**)&w.pin, pin_bytes, cudaHostAllocDefault) == cudaSuccess &&
+                cudaMalloc((void**)&w.dev, L.total) == cudaSuccess &&
+                cudaMalloc((void**)&w.x, sizeof(double) * n) == cudaSuccess &&
+                cudaMalloc((void**)&w.x_new, sizeof(double) * n) == cudaSuccess &&
+                cudaMalloc((void**)&w.step, sizeof(double) * n) == cudaSuccess &&
+                cudaMalloc((void**)&w.X0, sizeof(double) * 3 * P) == cudaSuccess;
+      w.device = a->device; w.pin_bytes = pin_bytes; w.dev_bytes = L.total; w.n = (size_t)n; w.p3 = (size_t)(3 * P);
+      if (!ok) { w.rc = BAX_E_CUDA; w.err = "bax_batch_solve: worker allocation failed"; failed.store(1); return; }
+      rc = bax_create(a->device, &w.h);
+      if (rc) { fail(rc, "bax_create"); return; }
+    }
+    bax_set_blocking_sync(w.h, block ? 1 : 0);
     for (;;) {
       if (failed.load()) return;
       const int k = next.fetch_add(1);
@@ -159,15 +196,22 @@ extern "C" int bax_batch_solve(const bax_batch_args* a) {
   for (auto& w : W) {
     if (w.rc && !rc_all) { rc_all = w.rc; msg = w.err; }
     if (w.s) cudaStreamSynchronize(w.s);
-    if (w.h) bax_destroy(w.h);
-    if (w.X0) cudaFree(w.X0);
-    if (w.step) cudaFree(w.step);
-    if (w.x_new) cudaFree(w.x_new);
-    if (w.x) cudaFree(w.x);
-    if (w.dev) cudaFree(w.dev);
-    if (w.pin) cudaFreeHost(w.pin);
-    if (w.s) cudaStreamDestroy(w.s);
+  }
+  {
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    for (auto& w : W) {
+      if (w.rc || !w.h || g_pool.size() >= 64) worker_free(w);     // a failed worker is not trusted again
+      else g_pool.push_back(w);
+    }
   }
   if (rc_all) { bax_set_error("bax_batch_solve: %s", msg.c_str()); return rc_all; }
+  return BAX_OK;
+}
+
+// Free the parked workers (streams, handles, pinned and device buffers) of earlier bax_batch_solve calls.
+extern "C" int bax_batch_release(void) {
+  std::lock_guard<std::mutex> lk(g_pool_mu);
+  for (auto& w : g_pool) worker_free(w);
+  g_pool.clear();
   return BAX_OK;
 }

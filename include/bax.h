@@ -178,6 +178,9 @@ typedef struct bax_batch_args {
                                     hosts with fewer cores than worker threads */
 } bax_batch_args;
 int bax_batch_solve(const bax_batch_args* a);
+/* The workers of a call (stream, handle, pinned staging, device buffers: ~60 ms to create twelve) are parked for the next
+ * call whose problems fit; this frees them. */
+int bax_batch_release(void);
 
 /* Weighted linear triangulation of every (frame, joint) — util.triangulate_with_conf,
  * reference util.py:325-354 (+ triangulate_point 308-322).  R [C][9], t [C][3]; X [N*J][3] (NaN where
