@@ -67,7 +67,8 @@ int rsx_calib_linear(rsx_handle* h, const uint8_t* mask3d, const uint8_t* mask2d
 
 /* HOST: the 6 smallest eigenvalues (Ritz values, ascending) of the normal matrix from the last rsx_calib_linear on this
  * handle — what the reference gets from eigh(subset_by_index=(0, 5)) and tests as w[3] / w[4] > 1e-4 for its
- * "degenerate case" warning (calib_linear.py:94-100). */
+ * "degenerate case" warning (calib_linear.py:94-100).  w[0..3] are converged (1e-9); w[4], w[5] are the Ritz values of
+ * the 6-dimensional iteration space at that moment: upper bounds of the true eigenvalues, typically within 10-20 %. */
 int rsx_calib_linear_eigs(rsx_handle* h, double* w_host /*[6]*/);
 
 /* DLT re-triangulation of all M ray sets under one model: calib_linear.py:127-133, i.e. pycalib.calib.triangulate

@@ -195,6 +195,29 @@ def test_ba_main_literal_vs_reference_literal(golden_dir, capsys):
     assert ang < 1e-3 and dt < 1e-3, (ang, dt)
 
 
+def test_initial_prior_prints_are_unscaled_also_for_zero_weights(golden_dir, capsys):
+    """ba_main prints the UNSCALED prior terms, as the reference does (ba.py:179-183: objfun_var3d / objfun_varbone
+    evaluated directly) — also when a weight is 0 and the term cannot be recovered from the weighted residual
+    (ADVICE r01)."""
+    g = np.load(os.path.join(golden_dir, "ba_small.npz"))
+    C = g["K"].shape[0]
+    vals = {}
+    for lam in ((1.0, 1.0), (0.0, 1.0), (1.0, 0.0)):
+        ba.ba_main(np.arange(C), g["K"], g["R_init"], g["t_init"], g["sp2d"], g["ss2d"], g["sp3d"], g["ss3d"], *lam,
+                   max_nfev=2)
+        out = capsys.readouterr().out
+        vals[lam] = [float(l.split(":")[1]) for l in out.splitlines() if l.startswith("Initial mean")]
+        assert len(vals[lam]) == 3
+    args = (g["K"], g["sp2d"].reshape(C, -1, 2), g["ss2d"], g["sp3d"], g["ss3d"], bo.OP_BONE, C, g["ss2d"].shape[1],
+            g["ss2d"].shape[2], 1.0, 1.0)
+    f = bo.objfun(g["theta0"], *args)
+    n_vis = int((g["ss2d"] > 0).sum())
+    B = len(bo.OP_BONE)
+    ref = [np.mean(f[:2 * n_vis] ** 2), np.mean(f[2 * n_vis:-B] ** 2), np.mean(f[-B:] ** 2)]
+    for lam, v in vals.items():
+        assert np.allclose(v, ref, rtol=1e-9, atol=0), (lam, v, ref)
+
+
 def test_nan_start_raises_like_reference():
     sc = scene.make_scene(C=4, N=4, seed=3)
     sp2d, ss2d, sp3d, ss3d = scene.ba_inputs(sc)

@@ -222,3 +222,26 @@ def test_fit_kernel_modes_agree(monkeypatch, mode):
     assert i0["best"] == i1["best"]
     assert np.array_equal(i0["mask_2d"], i1["mask_2d"]) and np.array_equal(i0["mask_3d"], i1["mask_3d"])
     assert np.max(np.abs(R0 - R1)) < 1e-8 and np.max(np.abs(t0 - t1)) < 1e-8
+
+
+def test_calib_linear_eigenvalues_and_warning(golden_dir, capsys):
+    """rsx_calib_linear_eigs: the six smallest eigenvalues of the normal matrix — what the reference reads from
+    eigh(subset_by_index=(0, 5)) and tests as w[3] / w[4] > 1e-4 (calib_linear.py:94-100) — against a dense eigh of the
+    oracle's matrix; the drop-in prints the reference's WARN exactly when that test fires."""
+    from calib_b200 import calib_linear as cl
+    g = np.load(os.path.join(golden_dir, "ransac_c4.npz"))
+    v, n = g["vc"], g["n"]
+    prob = cr.RansacProblem(v, n)
+    R, t, X, info = prob.calib_linear()
+    prob.close()
+    A = ro.translation_system(ro.rotations_from_directions(v), n)
+    w = np.linalg.eigvalsh(A.T @ A)[:6]
+    e = np.array(info["eigs"])
+    assert e.shape == (6,) and np.all(np.diff(e) >= -1e-12 * w[5])
+    assert np.max(np.abs(e[:4] - w[:4])) <= 1e-9 * w[5]          # the four wanted eigenvalues: converged
+    # the fifth and sixth are Ritz values of the 6-dimensional iteration space when the wanted four have settled:
+    # upper bounds of the true ones, good to a few 10 % — enough for a test against 1e-4
+    assert np.all(e[4:] >= w[4:] * (1 - 1e-9)) and np.all(e[4:] <= 1.5 * w[4:])
+    cl.calib_linear(v, n)
+    out = capsys.readouterr().out
+    assert ("WARN: degenerate case" in out) == bool(w[3] / w[4] > 1e-4)
