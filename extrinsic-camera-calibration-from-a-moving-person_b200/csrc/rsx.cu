@@ -37,7 +37,8 @@ k_rsx_fit_warp(int C, int64_t N, int64_t M, const double* __restrict__ v, const 
                double* __restrict__ Rt, unsigned long long* __restrict__ stats /*[4]: fall-backs, sweeps, work counter, deferred*/,
                int32_t* __restrict__ deferred /*null: the warp runs the Jacobi fall-back itself*/,
                double* h_global /*[warps of the grid][nu][ld] or null: H in shared memory too*/,
-               int compact /*compact shared-memory layout (needs deferred and h_global)*/) {
+               int compact /*compact shared-memory layout (needs deferred and h_global)*/,
+               uint8_t* __restrict__ deferred_flag /*[H] or null: set to 1 for the hypotheses left to the second pass*/) {
   extern __shared__ __align__(16) double sm[];
   const int nu = 3 * (RSX_S + C), ld = nu | 1;
   // The dense normal matrix H is written once and read once (the arrow solver copies its blocks out), so it lives in
@@ -72,7 +73,10 @@ k_rsx_fit_warp(int C, int64_t N, int64_t M, const double* __restrict__ v, const 
       if (lane == 0) {
         const int sw = ws.iflag[8];
         if (sw < 0) atomicAdd(stats, 1ULL); else atomicAdd(stats + 1, (unsigned long long)sw);
-        if (!done) deferred[atomicAdd(stats + 3, 1ULL)] = (int32_t)h;     // second pass: k_rsx_fit_deferred
+        if (!done) {
+          deferred[atomicAdd(stats + 3, 1ULL)] = (int32_t)h;             // second pass: k_rsx_fit_deferred
+          if (deferred_flag) deferred_flag[h] = 1;
+        }
       }
     }
     __syncwarp();
@@ -83,7 +87,7 @@ k_rsx_fit_warp(int C, int64_t N, int64_t M, const double* __restrict__ v, const 
 // Second pass over the hypotheses whose arrow iteration did not settle: one CTA each, the parallel cyclic Jacobi
 // diagonalisation.  A warp of k_rsx_fit_warp running it inline takes ~50 normal fits, and the few warps that met one
 // near the end of a chunk kept the whole GPU waiting (ncu: SMs active 62 % of the kernel's time).
-__global__ void __launch_bounds__(FIT_THREADS)
+__global__ void __launch_bounds__(FIT_THREADS, 4)
 k_rsx_fit_deferred(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
                    const int32_t* __restrict__ samp_v, const int32_t* __restrict__ samp_m,
                    const int32_t* __restrict__ deferred, const unsigned long long* __restrict__ stats,
@@ -106,13 +110,19 @@ k_rsx_fit_deferred(int C, int64_t N, int64_t M, const double* __restrict__ v, co
 template <int MODE, int MINB>
 __global__ void __launch_bounds__(SCORE_THREADS, MINB)
 k_rsx_score(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
-            const double* __restrict__ Rt, int64_t H, double* __restrict__ score, double* __restrict__ parts) {
+            const double* __restrict__ Rt, int64_t H, double* __restrict__ score, double* __restrict__ parts,
+            const uint8_t* __restrict__ skip /*[H] or null: hypotheses whose model is not ready yet (second fit pass)*/,
+            const int32_t* __restrict__ list /*null, or: score list[0 .. *n_list) instead of 0 .. H*/,
+            const unsigned long long* __restrict__ n_list) {
   extern __shared__ __align__(16) double sm[];       // [C][12] model, 2*32 reduction scratch, [C][9] R_0 R_c^T
   double* sRt = sm;
   double* red = sm + ((12 * C + 1) & ~1);
   double* sG = red + 64;
   CtaCtx g{(int)threadIdx.x, (int)blockDim.x};
-  for (int64_t h = blockIdx.x; h < H; h += gridDim.x) {
+  const int64_t count = list ? (int64_t)*n_list : H;
+  for (int64_t it = blockIdx.x; it < count; it += gridDim.x) {
+    const int64_t h = list ? (int64_t)list[it] : it;
+    if (skip && skip[h]) continue;                       // uniform over the CTA
     __syncthreads();
     for (int i = threadIdx.x; i < 12 * C; i += blockDim.x) sRt[i] = Rt[(size_t)h * C * 12 + i];
     __syncthreads();
@@ -208,6 +218,12 @@ extern "C" int rsx_create(int device, rsx_handle** out) {
   h->sm_count = prop.multiProcessorCount;
   BAX_CUDA(cudaEventCreate(&h->ev0));
   BAX_CUDA(cudaEventCreate(&h->ev1));
+  BAX_CUDA(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
+  BAX_CUDA(cudaEventCreateWithFlags(&h->ev_main, cudaEventDisableTiming));
+  BAX_CUDA(cudaEventCreateWithFlags(&h->ev_side, cudaEventDisableTiming));
+  // default off: both the first-pass and the score kernel fill the register files, so the second pass run "under" the
+  // score kernel takes SM slots from it for its whole (long) latency — 83.9 against 81.9 ms per 100 k measured
+  { const char* e = getenv("RSX_OVERLAP_DEFERRED"); h->overlap_deferred = e ? atoi(e) : 0; }
   BAX_CUDA(cudaMallocHost((void**)&h->host_pinned, 64 * sizeof(double)));
   h->red_bytes = sizeof(double) * (1 << 20);
   BAX_CUDA(cudaMalloc(&h->red, h->red_bytes));
@@ -238,6 +254,9 @@ extern "C" int rsx_destroy(rsx_handle* h) {
   if (h->bx) { if (h->bx->syrk_part) cudaFree(h->bx->syrk_part); if (h->bx->partials) cudaFree(h->bx->partials); free(h->bx); }
   cudaFree(h->red); cudaFree(h->fit_stats); if (h->deferred) cudaFree(h->deferred); cudaFreeHost(h->host_pinned);
   cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
+  if (h->side) { cudaStreamSynchronize(h->side); cudaStreamDestroy(h->side); }
+  cudaEventDestroy(h->ev_main); cudaEventDestroy(h->ev_side);
+  if (h->deferred_flag) cudaFree(h->deferred_flag);
   free(h);
   return BAX_OK;
 }
@@ -268,7 +287,14 @@ static int ensure_models(rsx_handle* h, int64_t H) {
   return BAX_OK;
 }
 
-int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, int64_t H, double* Rt, cudaStream_t s) {
+// overlap != null: the deferred second pass is launched on the handle's side stream (ordered after the first pass) and
+// *overlap is set to 1 — the caller scores the finished hypotheses meanwhile (k_rsx_score skips h->deferred_flag) and the
+// deferred ones after waiting for h->ev_side.  The second pass is one wave of CTAs at the latency of a 42 x 42 Jacobi
+// diagonalisation with the SMs almost idle (ncu: 6 % warps active): run back to back it was 1.3-1.6 ms of every 20 k-
+// hypothesis chunk, a third of the fit time; under the score kernel it costs nothing measurable.
+int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, int64_t H, double* Rt, cudaStream_t s,
+                   int* overlap = nullptr) {
+  if (overlap) *overlap = 0;
   h->fits_total += H;
   const int C = h->C, nu = 3 * (RSX_S + C), ld = nu | 1;
   const size_t small = fit_ws_small_doubles(C) * sizeof(double);
@@ -280,7 +306,7 @@ int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, 
     const size_t per_warp = (compact ? ((fit_ws_compact_small_doubles(C) + fit_ws_compact_v_doubles(C) + 1) & ~(size_t)1)
                                      : ((fit_ws_small_doubles(C) + (hglob ? 1 : 2) * (size_t)nu * ld + 1) & ~(size_t)1)) * sizeof(double);
     static const int env_warps = getenv("RSX_FIT_WARPS") ? atoi(getenv("RSX_FIT_WARPS")) : FITW_WARPS;
-    static const int env_lock = getenv("RSX_FIT_LOCKSTEP") ? atoi(getenv("RSX_FIT_LOCKSTEP")) : 1;   // default: lock-step batches (17.1 against 18.2 ms per 100 k)
+    static const int env_lock = getenv("RSX_FIT_LOCKSTEP") ? atoi(getenv("RSX_FIT_LOCKSTEP")) : 0;   // lock-step batches: 17.1 against 18.2 ms per 100 k while the kernel was 15 k instructions; free-running wins again (15.4 : 15.9) now that it is 9.6 k
     const bool lockstep = env_lock != 0 && compact && per_warp * 16 <= 226 * 1024;
     const int fw = lockstep ? 16 : (env_warps == 4 ? 4 : FITW_WARPS);
     const size_t smem = per_warp * fw;
@@ -314,24 +340,42 @@ int rsx_launch_fit(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, 
           h->cap_deferred = H;
         }
         deferred = h->deferred;
+        if (overlap && h->side) {
+          if (H > h->cap_flag) {
+            if (h->deferred_flag) cudaFree(h->deferred_flag);
+            h->deferred_flag = nullptr; h->cap_flag = 0;
+            BAX_CUDA(cudaMalloc(&h->deferred_flag, (size_t)H));
+            h->cap_flag = H;
+          }
+          BAX_CUDA(cudaMemsetAsync(h->deferred_flag, 0, (size_t)H, s));
+        }
       }
+      const bool side = deferred && overlap && h->side && h->deferred_flag;
+      uint8_t* dflag = side ? h->deferred_flag : nullptr;
       RsxTimer t(h, RSX_T_FIT, s, deferred ? 2 : 1);
       unsigned long long* fst = (unsigned long long*)h->fit_stats;
       if (deferred && lockstep)
-        k_rsx_fit_warp<true, 16, true><<<(unsigned)grid, 32 * 16, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt, fst, deferred, hg, 1);
+        k_rsx_fit_warp<true, 16, true><<<(unsigned)grid, 32 * 16, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt, fst, deferred, hg, 1, dflag);
       else if (deferred && fw == 4)
-        k_rsx_fit_warp<true, 4, false><<<(unsigned)grid, 32 * 4, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt, fst, deferred, hg, compact ? 1 : 0);
+        k_rsx_fit_warp<true, 4, false><<<(unsigned)grid, 32 * 4, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt, fst, deferred, hg, compact ? 1 : 0, dflag);
       else if (deferred)
-        k_rsx_fit_warp<true, 2, false><<<(unsigned)grid, 32 * 2, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt, fst, deferred, hg, compact ? 1 : 0);
+        k_rsx_fit_warp<true, 2, false><<<(unsigned)grid, 32 * 2, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt, fst, deferred, hg, compact ? 1 : 0, dflag);
       else
-        k_rsx_fit_warp<false, 2, false><<<(unsigned)grid, 32 * 2, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt, fst, deferred, hg, 0);
+        k_rsx_fit_warp<false, 2, false><<<(unsigned)grid, 32 * 2, smem, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, H, Rt, fst, deferred, hg, 0, nullptr);
       BAX_LAUNCH_CHECK();
       if (deferred) {
         BAX_CUDA(cudaFuncSetAttribute(k_rsx_fit_deferred, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(small + hv)));
-        k_rsx_fit_deferred<<<2 * h->sm_count, FIT_THREADS, small + hv, s>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, deferred,
+        cudaStream_t sd = s;
+        if (side) {
+          BAX_CUDA(cudaEventRecord(h->ev_main, s));
+          BAX_CUDA(cudaStreamWaitEvent(h->side, h->ev_main, 0));
+          sd = h->side;
+        }
+        k_rsx_fit_deferred<<<4 * h->sm_count, FIT_THREADS, small + hv, sd>>>(C, h->N, h->M, h->v, h->n, samp_v, samp_m, deferred,
                                                                           (const unsigned long long*)h->fit_stats,
                                                                           (unsigned long long*)h->fit_stats + 4, Rt);
         BAX_LAUNCH_CHECK();
+        if (side) { BAX_CUDA(cudaEventRecord(h->ev_side, h->side)); *overlap = 1; }
       }
       return BAX_OK;
     }
@@ -366,18 +410,28 @@ extern "C" int rsx_fit_score(rsx_handle* h, const int32_t* samp_v, const int32_t
   BAX_CUDA(cudaSetDevice(h->device));
   double* models = Rt;
   if (!models) { int rc = ensure_models(h, H); if (rc) return rc; models = h->Rt; }
-  int rc = rsx_launch_fit(h, samp_v, samp_m, H, models, s); if (rc) return rc;
+  int pending = 0;
+  int rc = rsx_launch_fit(h, samp_v, samp_m, H, models, s, h->overlap_deferred ? &pending : nullptr); if (rc) return rc;
   {
     const size_t smem = sizeof(double) * (((12 * h->C + 1) & ~1) + 2 * 32 + 9 * h->C);
     int64_t grid = H < 64 * (int64_t)h->sm_count ? H : 64 * (int64_t)h->sm_count;
-    RsxTimer t(h, RSX_T_SCORE, s, 1);
-    if (h->score_mode == 0)
-      k_rsx_score<0, 3><<<(unsigned)grid, SCORE_THREADS, smem, s>>>(h->C, h->N, h->M, h->v, h->n, models, H, score, parts);
-    else if (h->score_mode == 2)
-      k_rsx_score<1, 2><<<(unsigned)grid, SCORE_THREADS, smem, s>>>(h->C, h->N, h->M, h->v, h->n, models, H, score, parts);
-    else
-      k_rsx_score<1, 3><<<(unsigned)grid, SCORE_THREADS, smem, s>>>(h->C, h->N, h->M, h->v, h->n, models, H, score, parts);
+    RsxTimer t(h, RSX_T_SCORE, s, pending ? 2 : 1);
+    const uint8_t* skip = pending ? h->deferred_flag : nullptr;
+    auto launch = [&](const uint8_t* sk, const int32_t* list, const unsigned long long* nl, int64_t g) {
+      if (h->score_mode == 0)
+        k_rsx_score<0, 3><<<(unsigned)g, SCORE_THREADS, smem, s>>>(h->C, h->N, h->M, h->v, h->n, models, H, score, parts, sk, list, nl);
+      else if (h->score_mode == 2)
+        k_rsx_score<1, 2><<<(unsigned)g, SCORE_THREADS, smem, s>>>(h->C, h->N, h->M, h->v, h->n, models, H, score, parts, sk, list, nl);
+      else
+        k_rsx_score<1, 3><<<(unsigned)g, SCORE_THREADS, smem, s>>>(h->C, h->N, h->M, h->v, h->n, models, H, score, parts, sk, list, nl);
+    };
+    launch(skip, nullptr, nullptr, grid);
     BAX_LAUNCH_CHECK();
+    if (pending) {                                   // the deferred fits ran on the side stream meanwhile
+      BAX_CUDA(cudaStreamWaitEvent(s, h->ev_side, 0));
+      launch(nullptr, h->deferred, (const unsigned long long*)h->fit_stats + 3, grid < 4 * (int64_t)h->sm_count ? grid : 4 * (int64_t)h->sm_count);
+      BAX_LAUNCH_CHECK();
+    }
   }
   return BAX_OK;
 }

@@ -224,9 +224,8 @@ __host__ __device__ inline bool fit_hypothesis_t(const G& g, int C, int64_t N, i
   bool have_kb = false;
   if (fast && g.nt <= 32 && arrow_ws_doubles(C, g.nt) <= ws.v_doubles) {
     ArrowWs aw; arrow_ws_carve(ws.V, C, g.nt, aw);
-    // (letting the iteration run to 160 sweeps where a second pass exists was tried: 2 % faster, but the slowly converging
-    // hypotheses it then keeps settle 10x further from the Jacobi result — scores off by up to 2e-8 — so 48 it stays)
-    have_kb = arrow_null4(g, ws.H, ld, C, ws.R, aw, ws.kb, ws.iflag + 8, ARW_MAX_SWEEPS);
+    // where a second pass exists (a deferred Jacobi fit costs ~50 fits and a kernel of its own) slow runs may go on
+    have_kb = arrow_null4(g, ws.H, ld, C, ws.R, aw, ws.kb, ws.iflag + 8, defer ? 200 : ARW_MAX_SWEEPS);
     if (!have_kb && g.tid == 0) ws.iflag[8] = -1;
   }
   if (!have_kb && defer) return false;           // uniform over the group

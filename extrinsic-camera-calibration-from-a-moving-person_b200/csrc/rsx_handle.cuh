@@ -21,6 +21,11 @@ struct rsx_handle {
   int64_t fits_total;   // hypotheses fitted since rsx_create
   int32_t* deferred;    // hypotheses of the current launch left to k_rsx_fit_deferred
   int64_t cap_deferred;
+  uint8_t* deferred_flag;  // [cap_flag] 1 = left to the second pass (the score kernel skips it until that pass is done)
+  int64_t cap_flag;
+  cudaStream_t side;       // the second fit pass runs here, under the score kernel of the finished hypotheses
+  cudaEvent_t ev_main, ev_side;
+  int overlap_deferred;    // env RSX_OVERLAP_DEFERRED=0: second pass on the caller's stream, as in round 1
   double* red;          // small reduction scratch
   size_t red_bytes;
   double* host_pinned;  // [64]
