@@ -458,6 +458,9 @@ def run_gpu(args):
                 "gpu_launches": int(launches), "roofline": roofline, "roofline_step": roofline_step,
                 "sharded_parity": parity, "cpu_baseline": cpu, "comm": comm,
                 "clocks": sampler.summary()}
+    # ---------------- the other single-GPU BA configs, short runs (BASELINE configs[0] and [2]); one GPU only
+    if line is not None and world == 1 and not args.no_other:
+        line["other_configs"] = {name: other_config_leg(name, dev) for name in ("cfg1", "cfg3") if name != args.workload}
     # ---------------- RANSAC leg (hypotheses/s), BASELINE configs[1]
     from calib_b200 import calib_ransac as cr
     rs = cr.bench_leg(rank, world, dev, steps=max(1, min(args.steps, 3)), no_cpu=args.no_cpu or world > 1)
@@ -476,6 +479,53 @@ def run_gpu(args):
     prob.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def other_config_leg(name, dev, steps=30, warmup=3):
+    """BA observations/s per LM iteration on another BASELINE config (device-resident inputs, CUDA events, iterations of
+    complete solves with the reference's tolerances, as for the headline workload) + its k_rj fraction of the HBM peak."""
+    import torch
+    from calib_b200 import ba
+    sc, (sp2d, ss2d, sp3d, ss3d), w = make_workload(name, 1000)
+    C, N, J = ss2d.shape
+    prob = ba.BAProblem(sc.K, sp2d, ss2d, sp3d, ss3d, ba.OP_BONE, *w["lam"], device=dev)
+    try:
+        x0 = prob.triangulate(sc.R_init, sc.t_init)
+        theta0 = ba.to_theta(sc.R_init, sc.t_init, x0.reshape(-1, 3))
+        sol = ba.TRFSolver(prob, theta0)
+        its = 0
+
+        def step():
+            nonlocal sol
+            sol.iterate()
+            if sol.done():
+                sol = ba.TRFSolver(prob, theta0)
+        for _ in range(warmup):
+            step()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        out = prob.residual_jacobian(sol.x, with_index=False)
+        for _ in range(3):
+            prob.residual_jacobian(sol.x, with_index=False, out=out)
+        e0.record()
+        for _ in range(10):
+            prob.residual_jacobian(sol.x, with_index=False, out=out)
+        e1.record()
+        torch.cuda.synchronize()
+        ms_rj = e0.elapsed_time(e1) / 10
+        peak, _ = measured_peaks()
+        bpo = 184.0 + 24.0 / (prob.n_vis / float(prob.P))
+        return {"workload": w["name"], "observations": prob.n_vis, "value": prob.n_vis / (ms * 1e-3), "unit": "observations/s",
+                "ms_per_step": ms, "steps": steps, "k_rj_frac_of_hbm_peak": bpo * prob.n_vis / (ms_rj * 1e-3) / 1e9 / peak,
+                "k_rj_ms": ms_rj}
+    finally:
+        prob.close()
 
 
 def fp64_peaks():
@@ -705,6 +755,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference", "cpu_rows"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-cpu-rows", dest="no_cpu_rows", action="store_true", help="reference arm: skip the executed CPU rows")
+    ap.add_argument("--no-other", dest="no_other", action="store_true", help="skip the short cfg1 / cfg3 runs of the one-GPU line")
     ap.add_argument("--batch", type=int, default=512, help="problems per GPU of the sweep leg (0 = skip; 512 x 8 GPUs = BASELINE configs[4])")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":

@@ -231,3 +231,32 @@ def test_eval_align_vs_reference_golden(golden_dir, case):
     sc = scene.make_scene(**ast.literal_eval(str(g["scene_kw"])))
     nR, nt, _, _, _ = ev.align(sc.R_gt, sc.t_gt.reshape(-1, 3, 1), g["R"], g["t"], np.zeros((1, 3)))
     assert np.max(np.abs(nR - g["nR"])) < 1e-12 and np.max(np.abs(nt - g["nt"])) < 1e-12
+
+
+def test_sample_plan_caches_and_extends_the_reference_stream():
+    """SamplePlan (calib_ransac.py host side): the cached, pinned-when-possible copy of the reference's sample stream
+    (calib_ransac.py:148-151) — generated lazily in chunks, extended on demand, handed back on the next call with the same
+    (seed, N, M), and always equal to NumPy's own stream."""
+    from calib_b200 import calib_ransac as cr
+    cr.SamplePlan._cache.clear()
+    N, M, seed = 149, 325, 5
+    rng = np.random.default_rng(seed)
+    ref_n, ref_m = [], []
+    for _ in range(300):
+        ref_n.append(rng.choice(N, size=10, replace=False)); ref_m.append(rng.choice(M, size=10, replace=False))
+    ref_n, ref_m = np.array(ref_n), np.array(ref_m)
+    plan = cr.SamplePlan.get(N, M, seed, 100)
+    assert plan.done == 0
+    plan.ensure(40); plan.ensure(100)                      # two chunks
+    assert plan.done == 100 and np.array_equal(plan.sn[:100], ref_n[:100]) and np.array_equal(plan.sm[:100], ref_m[:100])
+    again = cr.SamplePlan.get(N, M, seed, 300)             # same key: the same plan, grown, earlier samples kept
+    assert again is plan and plan.done == 100
+    assert plan.ensure(300) > 0.0 and plan.ensure(300) == 0.0
+    assert np.array_equal(plan.sn[:300], ref_n) and np.array_equal(plan.sm[:300], ref_m)
+    other = cr.SamplePlan.get(N, M, seed + 1, 10)
+    assert other is not plan
+    for k in range(6):                                     # bounded cache
+        cr.SamplePlan.get(N + k + 1, M, seed, 10)
+    assert len(cr.SamplePlan._cache) <= cr.SamplePlan.MAX_CACHED
+    sn, sm = cr.sample_indices(N, M, 300, seed)
+    assert np.array_equal(sn, ref_n) and np.array_equal(sm, ref_m)
