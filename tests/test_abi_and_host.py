@@ -38,6 +38,25 @@ def test_library_exports_every_declared_symbol(header):
     assert set(names) <= bound, f"ctypes binding missing for {set(names) - bound}"
 
 
+def test_new_entry_points_reject_bad_arguments_without_touching_the_gpu():
+    """Argument checks of the round-2 entry points (no device work happens before them): error code + message."""
+    import ctypes as C_
+    L = _lib.lib()
+    assert L.bax_batch_solve(None) == -1 and b"bax_batch_solve" in L.bax_last_error()
+    a = _lib.BatchArgs()
+    a.n_problems, a.C, a.N, a.J = 3, 4, 10, 17                    # no pointers filled in
+    assert L.bax_batch_solve(C_.byref(a)) == -1
+    st = (C_.c_int64 * 4)()
+    assert L.rsx_fit_stats(None, st, None) == -1 and b"rsx_fit_stats" in L.bax_last_error()
+    assert L.bax_comm_stats(None, st) == -1
+    assert L.bax_allreduce_attach(None, None) == -1
+    assert L.bax_set_blocking_sync(None, 1) == -1
+    assert L.bax_comm_unique_id(None) != 0
+    w = (C_.c_double * 6)()
+    assert L.rsx_calib_linear_eigs(None, w) == -1
+    assert L.bax_batch_release() == 0                            # nothing parked: a no-op
+
+
 def test_no_cpu_fallback_without_gpu():
     import torch
     if torch.cuda.is_available():
