@@ -119,7 +119,8 @@ def _native_comm(group, dev):
     import torch.distributed as dist
     if os.environ.get("BAX_NATIVE_COMM", "1") == "0" or dist.get_backend(group) != "nccl":
         return None
-    key = (id(group), dev.index)
+    # keyed by the group's MEMBERS (global ranks), not by id(group): a destroyed group's id can come back on another object
+    key = (tuple(dist.get_process_group_ranks(group)), dev.index)
     if key not in _native_comms:
         L = lib()
         rank, world = dist.get_rank(group), dist.get_world_size(group)
