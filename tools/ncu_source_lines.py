@@ -34,5 +34,7 @@ for l in sass[start:end]:
             agg[cur] += ex[off]; samp[cur] += sm[off]; stat[cur] += 1
 tot, tots = sum(agg.values()), sum(samp.values())
 print(f"kernel {prefix}: {tot} executed warp-instructions, {tots} samples, {sum(stat.values())} SASS instructions matched")
+import signal
+signal.signal(signal.SIGPIPE, signal.SIG_DFL)
 for (f, ln), c in agg.most_common(40):
     print(f"{f}:{ln:<5d} executed {100 * c / tot:5.1f} %  samples {100 * samp[(f, ln)] / max(tots, 1):5.1f} %  static {stat[(f, ln)]}")
