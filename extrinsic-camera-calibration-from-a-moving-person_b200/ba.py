@@ -853,17 +853,21 @@ def _ba_batch_native(idx, problems, lambda1, lambda2, n_workers, ftol=1e-4, xtol
         theta = np.empty((n, npar))
         info = np.zeros((n, 8))
         a = _lib.BatchArgs()
-        # worker threads spin on their scalar read-backs: give every one a core.  With several ranks on one host
-        # (LOCAL_WORLD_SIZE) the cores are shared: 4 ranks x 12 workers on a 24-core box ran at a third of the single-rank
-        # rate.  Fewer workers first; sleeping waits only if even two workers per rank oversubscribe the host.
+        # worker threads spin on their scalar read-backs: one per core this rank can have.  With several ranks on one
+        # host (LOCAL_WORLD_SIZE) the cores are shared: 4 ranks x 12 spinning workers on a small host ran at a third of
+        # the single-rank rate.  Measured with 4 cores per rank: 3 workers 957, 4 workers 1163, 8 workers 1099 problems/s
+        # per rank spinning; sleeping waits (bax_set_blocking_sync) 627 / 744 / 996 — so: spin, workers = cores per rank
+        # (at least 4), sleep only when even that oversubscribes the host twice over.
         try:
             cpus = len(os.sched_getaffinity(0))
         except AttributeError:
             cpus = os.cpu_count() or 1
         local_world = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
-        fair = max(2, cpus // local_world - 1)
-        nw = max(1, min(int(n_workers), fair))
-        a.blocking_sync = 1 if nw * local_world > cpus else 0
+        nw = max(1, min(int(n_workers), max(4, cpus // local_world)))
+        a.blocking_sync = 1 if nw * local_world > 2 * cpus else 0
+        if os.environ.get("BAX_BATCH_FORCE_WORKERS"):             # experiments: fixed worker count / wait mode
+            nw = int(os.environ["BAX_BATCH_FORCE_WORKERS"])
+            a.blocking_sync = 1 if os.environ.get("BAX_BATCH_BLOCK", "0") == "1" else 0
         a.n_problems, a.n_workers, a.device = n, nw, dev
         a.C, a.N, a.J, a.J3, a.B = Cn, N, J, J3 or J, int(bones.shape[0])
         pK, py, ps_, pR, pt = ptrs(cols["K"]), ptrs(cols["y"]), ptrs(cols["s"]), ptrs(cols["R"]), ptrs(cols["t"])

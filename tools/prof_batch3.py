@@ -17,9 +17,10 @@ probs = [scenes[k % 16] for k in range(768)]
 ba.ba_batch(probs[:48], 1.0, 1.0, n_streams=12)
 if rank == 0:
     print("cpus", os.cpu_count(), "affinity", len(os.sched_getaffinity(0)), flush=True)
-for nw in (4, 8, 12):
+for nw in [int(x) for x in os.environ.get("WORKERS", "4,8,12").split(",")]:
     if world > 1:
         dist.barrier()
+    os.environ["BAX_BATCH_FORCE_WORKERS"] = str(nw)
     t0 = time.perf_counter(); ba.ba_batch(probs, 1.0, 1.0, n_streams=nw); dt = time.perf_counter() - t0
     print(f"rank {rank} workers {nw}: {len(probs) / dt:.0f} problems/s", flush=True)
 if world > 1:
