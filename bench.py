@@ -670,7 +670,9 @@ def batch_leg(rank, world, group, n_per_gpu=512, n_streams=12, n_distinct=64):
         dist.all_reduce(s)
         work, iters = float(s[0]), float(s[1])
     res = {"metric": "BA problems/s (complete ba_main runs, host arrays in / out)", "value": n / t_multi, "unit": "problems/s",
-           "problems": n, "problems_per_gpu": n_per_gpu, "distinct_scenes_per_gpu": n_distinct, "workers_per_gpu": n_streams,
+           "problems": n, "problems_per_gpu": n_per_gpu, "distinct_scenes_per_gpu": n_distinct,
+           "workers_per_gpu": ba.batch_stats.get("workers", n_streams), "workers_requested": n_streams,
+           "host": {k: ba.batch_stats.get(k) for k in ("cpus", "local_world", "blocking_sync")},
            "wall_s": t_multi, "lm_iterations": iters, "observations_per_s_per_lm_iteration": work / t_multi,
            "config": {"workload": "cfg5: independent 4-camera x 1000-frame x 17-joint problems, 512 per GPU (8 GPUs = the 4096 "
                                   "of BASELINE configs[4])",

@@ -809,6 +809,9 @@ def _worker_stream(dev, i):
     return pool[i]
 
 
+batch_stats = {}          # what the last native sweep of this process used: workers per GPU, wait mode, cores seen
+
+
 def _ba_batch_native(idx, problems, lambda1, lambda2, n_workers, ftol=1e-4, xtol=1e-8, gtol=1e-8, max_nfev=None,
                      return_info=False):
     """The sweep behind ONE C call per problem shape (bax_batch_solve, csrc/bax_batch.cu): native worker threads, each
@@ -869,6 +872,7 @@ def _ba_batch_native(idx, problems, lambda1, lambda2, n_workers, ftol=1e-4, xtol
             nw = int(os.environ["BAX_BATCH_FORCE_WORKERS"])
             a.blocking_sync = 1 if os.environ.get("BAX_BATCH_BLOCK", "0") == "1" else 0
         a.n_problems, a.n_workers, a.device = n, nw, dev
+        batch_stats.update(workers=nw, blocking_sync=int(a.blocking_sync), cpus=cpus, local_world=local_world)
         a.C, a.N, a.J, a.J3, a.B = Cn, N, J, J3 or J, int(bones.shape[0])
         pK, py, ps_, pR, pt = ptrs(cols["K"]), ptrs(cols["y"]), ptrs(cols["s"]), ptrs(cols["R"]), ptrs(cols["t"])
         prv = (C.c_void_p * n)(*[rvec[i].ctypes.data for i in range(n)])
