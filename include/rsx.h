@@ -48,6 +48,21 @@ int rsx_fit_score(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, i
  * best_host[0] = index or -1, score_host[0] = its score. Synchronises. */
 int rsx_argmin(rsx_handle* h, const double* score, int64_t H, int64_t* best_host, double* score_host, void* stream);
 
+/* The same search for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * No handle, and no cudaMalloc / cudaFree / allocating library call inside: the per-CTA partial winners live in a
+ * file-scope static device array of RSX_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.
+ *   device  CUDA device ordinal the pointers belong to
+ *   score   device [H], 1 <= H <= RSX_STATIC_MAX_H; a larger H is rejected with BAX_E_ARG (use rsx_argmin)
+ *   out     device [2] = { (double) index of the first minimum or -1, its score (+inf if none) }
+ * Asynchronous on `stream`; does not synchronise.  The first call on a device looks the array's address up
+ * (cudaGetSymbolAddress): make it once before any graph capture.  All calls share the one array per device: calls that
+ * overlap on the same GPU race and must be ordered by the caller (one stream, or events). */
+#define RSX_STATIC_CHUNK 4096                   /* scores per CTA = scores per scratch entry */
+#define RSX_STATIC_MAX_H (1 << 24)              /* 16 777 216 scores = 4096 scratch entries */
+#define RSX_STATIC_SCRATCH_BYTES 65792          /* 256 (arrival counter) + 4096 x (8 + 8) */
+int rsx_argmin_static(int device, const double* score, int64_t H, double* out, void* stream);
+
 /* Inlier masks of one model (calib_ransac.py:193-204):  mask2d[i] = all_c K00[c] * ||e_ci[:2]|| <= th2d,
  * mask3d[i] = e3d_i <= th3d.   Rt device [C][12]; K00 device [C]; mask2d uint8 [M], mask3d uint8 [N];
  * e_out [M][C][3] and e3d_out [N] optional (NULL).  counts_host[0..1] = inliers 2-D, 3-D. Synchronises. */
