@@ -543,14 +543,17 @@ def syrk_roofline(prob, sol, ms_step, C):
     """k_syrk96 against the FP64 tensor (DMMA) peak: timed live with CUDA events (the library's own per-family event
     timers) over damped solves at the current linearisation, so the bucket holds only the trial SYRK (k_syrk96 + its two
     split-K reduction kernels, microseconds).  Algorithmic flops = the lower triangle incl. diagonal of the
-    (6C+B+1)^2 product over K = 3P columns; issued = what the 96x96 tiles execute (padding + full diagonal tiles)."""
+    (6C+B+1)^2 product over K = 3P columns; issued = what the 96x96 tiles execute: 144 m8n8 accumulator tiles per
+    off-diagonal tile, and per diagonal tile the 78 of its lower triangle + 24 of the extras panel (+ 4 for the extras
+    corner in tile 0) — padding rows and the upper halves of the 8x8 tiles on the diagonal included."""
     import torch
     dmma, dfma, src = fp64_peaks()
     n_red = 6 * C + 12 + 1
     K = 3 * prob.P
     nt = (6 * C + 95) // 96
     tiles = nt * (nt + 1) // 2
-    issued = tiles * 96.0 * 96.0 * K * 2.0
+    mma_tiles = (tiles - nt) * 144 + nt * (78 + 24) + 4
+    issued = mma_tiles * 64.0 * K * 2.0
     algorithmic = n_red * (n_red + 1) / 2.0 * K * 2.0
     alpha = 0.01 * sol.g_2 / max(sol.x_norm, 1e-300)
     prob.timing(True)
@@ -566,7 +569,7 @@ def syrk_roofline(prob, sol, ms_step, C):
             "peak": dmma, "unit": "TFLOP/s", "frac": algorithmic / (ms * 1e-3) / 1e12 / dmma, "traffic": None,
             "issued_tflops": issued / (ms * 1e-3) / 1e12, "issued_frac": issued / (ms * 1e-3) / 1e12 / dmma,
             "dfma_peak": dfma, "peak_source": src, "flops_per_launch_algorithmic": algorithmic,
-            "flops_per_launch_issued": issued, "tiles_96x96": tiles, "k_columns": K, "reduced_size": n_red,
+            "flops_per_launch_issued": issued, "tiles_96x96": tiles, "diagonal_tiles": nt, "mma_tiles_m8n8": mma_tiles, "k_columns": K, "reduced_size": n_red,
             "ms_per_launch": ms, "launches_per_solve": t["syrk"][1] // reps, "share_of_step": ms / ms_step,
             "in_timed_step": True}
 
