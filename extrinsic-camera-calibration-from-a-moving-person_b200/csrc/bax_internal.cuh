@@ -77,6 +77,8 @@ struct bax_handle {
   int64_t ldv;
   double* syrk_part;         // split-K partial tiles
   size_t syrk_part_bytes;
+  double* lin_part;          // per-chunk camera sums of k_lin_fused [chunks][C][28]
+  size_t lin_part_bytes;
   double* dense_ws;          // S factor (6C x 6C), Z (B x 6C), LT (B x B), pc, w, misc
   double* coef;              // [6C + B] coefficients for back-substitution
   double* lin_stage;         // [<= 4096] scalars of a linearisation gathered for one device -> host copy

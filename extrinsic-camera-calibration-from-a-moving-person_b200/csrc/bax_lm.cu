@@ -304,6 +304,106 @@ k_lin_pt(const double* __restrict__ campack, const double* __restrict__ x, const
   for (int k = 0; k < 3; ++k) gp[3 * p + k] = g[k];
 }
 
+// k_lin_cam_mma and k_lin_pt in one pass: both linearise every observation (reading s, y and x again), one to sum over
+// the points of a camera, the other over the cameras of a point.  Here a thread owns R points (as in k_lin_pt: V_p and
+// g_p stay in its registers over the camera loop) and a CTA owns the 128 R points of a chunk; per camera each warp folds
+// its 32 R observations into the 8 x 8 tile [J_c | e]^T [J_c | e] with DMMA exactly as k_lin_cam_mma does, the four warps'
+// tiles meet in shared memory (double-buffered: one CTA barrier per camera) and the 28 packed values go to
+// part[chunk][c][28].  The order of the additions inside V_p / g_p is that of k_lin_pt; the camera sums are cut into
+// chunks of points instead of grid strides, so they differ from k_lin_cam_mma's in the last bits.
+template <int R>
+__global__ void __launch_bounds__(128, 4)
+k_lin_fused(const double* __restrict__ campack, const double* __restrict__ x, const double2* __restrict__ y,
+            const double* __restrict__ s, int64_t P, int C, double* __restrict__ Vp, double* __restrict__ gp,
+            double* __restrict__ part /*[gridDim.x][C][28]*/) {
+  extern __shared__ __align__(16) double smf[];  // cams [C][CAMPACK] | X [4][8 LCM_LD] | red [2][4][64]
+  double* cams = smf;
+  double* Xall = smf + C * CAMPACK;
+  double* red = Xall + 4 * 8 * LCM_LD;
+  for (int i = threadIdx.x; i < C * CAMPACK; i += blockDim.x) cams[i] = campack[i];
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double* Xw = Xall + warp * 8 * LCM_LD;
+  int64_t pt[R]; bool in[R];
+  double px[R][3], V[R][6], g[R][3];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    pt[r] = ((int64_t)blockIdx.x * R + r) * 128 + threadIdx.x;
+    in[r] = pt[r] < P;
+    const int64_t q = in[r] ? pt[r] : P - 1;
+    px[r][0] = x[3 * q]; px[r][1] = x[3 * q + 1]; px[r][2] = x[3 * q + 2];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) V[r][k] = 0.0;
+    g[r][0] = g[r][1] = g[r][2] = 0.0;
+    if (!in[r]) pt[r] = P - 1;                   // loads stay in range; the score is forced to zero below
+  }
+  // (score, 2-D point) of the next camera are in flight while this one is worked on
+  double sc_n[R]; double2 yy_n[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) { sc_n[r] = s[pt[r]]; yy_n[r] = y[pt[r]]; }
+  for (int c = 0; c < C; ++c) {
+    double acc[2] = {0.0, 0.0};
+    const int cn = c + 1 < C ? c + 1 : c;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const double sc = in[r] ? sc_n[r] : 0.0; const double2 yy = yy_n[r];
+      sc_n[r] = s[(size_t)cn * P + pt[r]]; yy_n[r] = y[(size_t)cn * P + pt[r]];
+      double j0[8] = {0, 0, 0, 0, 0, 0, 0, 0}, j1[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      if (sc > 0) {
+        ObsLin o;
+        obs_linearize<true>(cams + c * CAMPACK, px[r][0], px[r][1], px[r][2], yy.x, yy.y, sc, o);
+        V[r][0] += o.jp[0][0] * o.jp[0][0] + o.jp[1][0] * o.jp[1][0];
+        V[r][1] += o.jp[0][0] * o.jp[0][1] + o.jp[1][0] * o.jp[1][1];
+        V[r][2] += o.jp[0][0] * o.jp[0][2] + o.jp[1][0] * o.jp[1][2];
+        V[r][3] += o.jp[0][1] * o.jp[0][1] + o.jp[1][1] * o.jp[1][1];
+        V[r][4] += o.jp[0][1] * o.jp[0][2] + o.jp[1][1] * o.jp[1][2];
+        V[r][5] += o.jp[0][2] * o.jp[0][2] + o.jp[1][2] * o.jp[1][2];
+#pragma unroll
+        for (int q = 0; q < 3; ++q) g[r][q] += o.jp[0][q] * o.e0 + o.jp[1][q] * o.e1;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { j0[k] = o.jr[0][k]; j0[3 + k] = o.jt[0][k]; j1[k] = o.jr[1][k]; j1[3 + k] = o.jt[1][k]; }
+        j0[6] = o.e0; j1[6] = o.e1;
+      }
+#pragma unroll
+      for (int col = 0; col < 8; ++col)
+        *reinterpret_cast<double2*>(Xw + col * LCM_LD + 2 * lane) = make_double2(j0[col], j1[col]);
+      __syncwarp();
+      const double* src = Xw + (lane >> 2) * LCM_LD + (lane & 3);
+#pragma unroll
+      for (int kk = 0; kk < 16; ++kk) {
+        const double v = src[4 * kk];
+        lcm_dmma(acc, v, v);
+      }
+      __syncwarp();
+    }
+    // acc = tile[lane>>2][2 (lane&3) + {0,1}] of this warp for camera c
+    double* rd = red + (c & 1) * 256;
+    *reinterpret_cast<double2*>(rd + warp * 64 + (lane >> 2) * 8 + 2 * (lane & 3)) = make_double2(acc[0], acc[1]);
+    __syncthreads();                              // the other buffer is not written again before the next barrier
+    if (threadIdx.x < 28) {
+      int a, b;
+      if (threadIdx.x < 21) {                     // k-th entry of the upper triangle of the 6 x 6 block, row-major
+        int k = threadIdx.x; a = 0;
+        while (k >= 6 - a) { k -= 6 - a; ++a; }
+        b = a + k;
+      } else if (threadIdx.x < 27) { a = threadIdx.x - 21; b = 6; }
+      else { a = 6; b = 6; }
+      double v = 0.0;
+#pragma unroll
+      for (int w = 0; w < 4; ++w) v += rd[w * 64 + a * 8 + b];
+      part[((size_t)blockIdx.x * C + c) * 28 + threadIdx.x] = v;
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    if (!in[r]) continue;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) Vp[6 * pt[r] + k] = V[r][k];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) gp[3 * pt[r] + k] = g[r][k];
+  }
+}
+
 // scatter the per-camera sums and the orientation-row SYRK into the packed LIN buffer
 //   lin = [ Hcc (6C x 6C) | gc (6C) | ssq_b (B) | sum e^2 | sum r_v3d^2 ]
 __global__ void k_lin_pack(const double* __restrict__ camsum /*[C][28]*/, const double* __restrict__ v3d /*[(3C+1)^2] or null*/,
@@ -437,27 +537,46 @@ extern "C" int bax_linearize_mid(bax_handle* h, void* stream) {
   int rc;
   {
     BaxTimer t(h, BAX_T_LIN, s, 6);
-    int g = obs_grid(h);
-    double* part = h->partials;                  // [g][C][28]
-    if ((size_t)g * C * 28 * sizeof(double) > h->partials_bytes / 4) { bax_set_error("partials overflow"); return BAX_E_STATE; }
-    // BAX_LINCAM: tuning knob — 4 (default) = DMMA kernel; 0..3 = DFMA kernel at 256x1, 128x3, 256x2, 128x4 CTAs/SM
-    static const int lc_variant = getenv("BAX_LINCAM") ? atoi(getenv("BAX_LINCAM")) : 4;
-    if (lc_variant >= 4) {                       // one wave of 4 resident CTAs per SM
-      int gm = (4 * h->sm_count) / C; if (gm < 1) gm = 1;
-      int nb128 = (int)((h->P + 127) / 128);
-      g = gm < nb128 ? gm : nb128;
-    }
-    if (lc_variant == 0) k_lin_cam<256, 1><<<dim3(g, C), 256, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
-    else if (lc_variant == 1) k_lin_cam<128, 3><<<dim3(g, C), 128, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
-    else if (lc_variant == 2) k_lin_cam<256, 2><<<dim3(g, C), 256, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
-    else if (lc_variant == 3) k_lin_cam<128, 4><<<dim3(g, C), 128, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
-    else k_lin_cam_mma<<<dim3(g, C), 32 * LCM_WARPS, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
-    BAX_LAUNCH_CHECK();
+    // BAX_LINCAM: tuning knob — 5 (default) = fused camera + point kernel (0.944 -> 0.827 ms per linearisation at the
+    // cfg4 shard, 0.351 -> 0.292 at cfg3, unchanged at 4 cameras); 4 = DMMA camera kernel + k_lin_pt;
+    // 0..3 = DFMA camera kernel at 256x1, 128x3, 256x2, 128x4 CTAs/SM + k_lin_pt
+    static const int lc_variant = getenv("BAX_LINCAM") ? atoi(getenv("BAX_LINCAM")) : 5;
     double* camsum = h->partials + (1 << 20);    // [C][28]
-    rc = bax_reduce_partials(h, part, g, C * 28, camsum, s); if (rc) return rc;
-    int nbp = (int)((h->P + 127) / 128);
-    k_lin_pt<<<nbp, 128, C * CAMPACK * sizeof(double), s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, h->Vp, h->gp);
-    BAX_LAUNCH_CHECK();
+    const int nbp = (int)((h->P + 127) / 128);
+    if (lc_variant >= 5) {
+      // one round of 128 points per CTA: two rounds (half the partials, 18 more accumulator registers) measured
+      // 0.842 against 0.827 ms per linearisation at 64 cameras, 0.312 against 0.292 at 31
+      const int g = nbp;
+      const size_t need = sizeof(double) * (size_t)g * C * 28;
+      if (need > h->lin_part_bytes) {
+        bax_dev_free(h, h->lin_part); h->lin_part = nullptr; h->lin_part_bytes = 0;
+        BAX_ALLOC(h, h->lin_part, need);
+        BAX_CUDA(cudaStreamSynchronize(h->mem_stream));
+        h->lin_part_bytes = need;
+      }
+      const size_t smem = sizeof(double) * ((size_t)C * CAMPACK + 4 * 8 * LCM_LD + 2 * 256);
+      BAX_CUDA(cudaFuncSetAttribute(k_lin_fused<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      k_lin_fused<1><<<g, 128, smem, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, h->Vp, h->gp, h->lin_part);
+      BAX_LAUNCH_CHECK();
+      rc = bax_reduce_partials(h, h->lin_part, g, C * 28, camsum, s); if (rc) return rc;
+    } else {
+      int g = obs_grid(h);
+      double* part = h->partials;                  // [g][C][28]
+      if ((size_t)g * C * 28 * sizeof(double) > h->partials_bytes / 4) { bax_set_error("partials overflow"); return BAX_E_STATE; }
+      if (lc_variant >= 4) {                       // one wave of 4 resident CTAs per SM
+        int gm = (4 * h->sm_count) / C; if (gm < 1) gm = 1;
+        g = gm < nbp ? gm : nbp;
+      }
+      if (lc_variant == 0) k_lin_cam<256, 1><<<dim3(g, C), 256, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
+      else if (lc_variant == 1) k_lin_cam<128, 3><<<dim3(g, C), 128, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
+      else if (lc_variant == 2) k_lin_cam<256, 2><<<dim3(g, C), 256, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
+      else if (lc_variant == 3) k_lin_cam<128, 4><<<dim3(g, C), 128, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
+      else k_lin_cam_mma<<<dim3(g, C), 32 * LCM_WARPS, 0, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, part);
+      BAX_LAUNCH_CHECK();
+      rc = bax_reduce_partials(h, part, g, C * 28, camsum, s); if (rc) return rc;
+      k_lin_pt<<<nbp, 128, C * CAMPACK * sizeof(double), s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, h->Vp, h->gp);
+      BAX_LAUNCH_CHECK();
+    }
     rc = bax_bone_pass2(h, h->theta_lin, lin + (size_t)C6 * C6 + C6, s); if (rc) return rc;
   }
   double* v3d = nullptr;

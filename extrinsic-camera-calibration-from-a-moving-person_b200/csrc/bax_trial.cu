@@ -10,6 +10,7 @@
 //   [ G^T    T-I    h0   ]      pc = S^-1 (-gc - rhs0 + G T^-1 h0)
 //   [ rhs0^T h0^T    .   ]      w  = T^-1 (h0 - G^T pc),  L_p^T p_p = bt_p - Y_p^T pc - Ut_p w
 #include "bax_internal.cuh"
+#include <stdlib.h>
 
 __device__ __forceinline__ void bone_u_dev(const double* __restrict__ x, int64_t frame_base3,
                                            const int32_t* __restrict__ bones, int b, int sgn,
@@ -43,6 +44,10 @@ k_build_yhat(const double* __restrict__ campack, const double* __restrict__ x, c
   for (int k = 0; k < 6; ++k) V[k] = Vp[6 * p + k];
   const Chol3r L = chol3r(V, alpha);
   double* col = Yhat + 3 * p;
+  // blockIdx.y = camera group: the cameras of a point are dealt over gridDim.y threads (of different CTAs) so that the
+  // grid is many short CTAs instead of 2.2 waves of long ones (see bax_trial_begin); group 0 also writes bt and Ut
+  const int c_lo = (int)(((int64_t)C * blockIdx.y) / gridDim.y), c_hi = (int)(((int64_t)C * (blockIdx.y + 1)) / gridDim.y);
+  if (blockIdx.y == 0) {
   {  // bt = L^-1 (-g_p)
     double a = -gp[3 * p], b = -gp[3 * p + 1], d = -gp[3 * p + 2];
     chol3r_fwd(L, a, b, d);
@@ -63,22 +68,23 @@ k_build_yhat(const double* __restrict__ campack, const double* __restrict__ x, c
       }
     }
   }
+  }
   // the (score, 2-D point) of the next BAX_PF cameras are in flight while this one is worked on:
   // a score-then-point load chain per camera left the kernel waiting on memory (ncu: long_scoreboard on top)
   double sc_q[BAX_PF]; double2 yy_q[BAX_PF];
 #pragma unroll
   for (int k = 0; k < BAX_PF; ++k) {
-    const int cc = k < C ? k : C - 1;
+    const int cc = c_lo + k < c_hi ? c_lo + k : c_hi - 1;
     sc_q[k] = s[(size_t)cc * P + p]; yy_q[k] = y[(size_t)cc * P + p];
   }
-  for (int c0 = 0; c0 < C; c0 += BAX_PF) {
+  for (int c0 = c_lo; c0 < c_hi; c0 += BAX_PF) {
 #pragma unroll
    for (int k = 0; k < BAX_PF; ++k) {           // ring slot k is a compile-time index: the queue stays in registers
     const int c = c0 + k;
-    if (c >= C) break;
+    if (c >= c_hi) break;
     const double sc = sc_q[k]; const double2 yy = yy_q[k];
     {
-      const int cn = c + BAX_PF < C ? c + BAX_PF : C - 1;
+      const int cn = c + BAX_PF < c_hi ? c + BAX_PF : c_hi - 1;
       sc_q[k] = s[(size_t)cn * P + p]; yy_q[k] = y[(size_t)cn * P + p];
     }
     if (!(sc > 0)) continue;                     // rows of unseen cameras stay zero (buffer is zero-initialised)
@@ -190,7 +196,14 @@ extern "C" int bax_trial_begin(bax_handle* h, double alpha, void* stream) {
     BaxTimer t(h, BAX_T_BUILD, s, 1);
     int nb = (int)((h->P + 127) / 128);
     double scale = h->lam2 * 2.0 / (double)h->n_frames_global;
-    k_build_yhat<<<nb, 128, C * CAMPACK * sizeof(double), s>>>(h->campack_lin, h->theta_lin + 6 * C, (const double2*)h->y2d,
+    // Every CTA does the same work and they all start together, so the grid finishes in ceil(CTAs / resident CTAs)
+    // rounds: 1661 CTAs on 5 x 148 slots are 2.24 -> 3 rounds, a quarter of the last one idle (ncu: SMs active 85 %).
+    // Dealing the cameras of a point over `groups` CTAs shortens the rounds, but every group repeats the point's loads
+    // and Cholesky and writes its own rows: measured at 64 cameras 0.474 / 0.413 / 0.446 / 0.493 ms for 1 / 2 / 4 / 8
+    // groups (0.456 before the change), at 16 cameras 0.138 / 0.126 / 0.135 / 0.146, at 31 and at 4 cameras flat.
+    static const int forced = getenv("BAX_YHAT_GROUPS") ? atoi(getenv("BAX_YHAT_GROUPS")) : 0;   // tuning aid
+    const int groups = forced > 0 && forced <= C ? forced : (C >= 16 ? 2 : 1);
+    k_build_yhat<<<dim3(nb, groups), 128, C * CAMPACK * sizeof(double), s>>>(h->campack_lin, h->theta_lin + 6 * C, (const double2*)h->y2d,
         h->s2d, h->P, C, h->J, h->B, h->bones, h->joint_bones, h->Lbar, scale, h->Vp, h->gp, alpha, h->Yhat, h->ldy);
     BAX_LAUNCH_CHECK();
   }
