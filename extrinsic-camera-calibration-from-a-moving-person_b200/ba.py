@@ -830,10 +830,31 @@ def _ba_batch_native(idx, problems, lambda1, lambda2, n_workers, ftol=1e-4, xtol
         groups.setdefault(key, []).append(k)
     out = {}
     bones = np.ascontiguousarray(OP_BONE, dtype=np.int32)
-    for (Cn, C2, N, J, J3), ks in groups.items():
+    # worker threads spin on their scalar read-backs: one per core this rank can have.  With several ranks on one
+    # host (LOCAL_WORLD_SIZE) the cores are shared: 4 ranks x 12 spinning workers on a small host ran at a third of
+    # the single-rank rate.  Measured with 4 cores per rank: 3 workers 957, 4 workers 1163, 8 workers 1099 problems/s
+    # per rank spinning; sleeping waits (bax_set_blocking_sync) 627 / 744 / 996 — so: spin, workers = cores per rank
+    # (at least 4), sleep only when even that oversubscribes the host twice over.
+    try:
+        cpus = len(os.sched_getaffinity(0))
+    except AttributeError:
+        cpus = os.cpu_count() or 1
+    local_world = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
+    nw = max(1, min(int(n_workers), max(4, cpus // local_world)))
+    blocking = 1 if nw * local_world > 2 * cpus else 0
+    if os.environ.get("BAX_BATCH_FORCE_WORKERS"):             # experiments: fixed worker count / wait mode
+        nw = int(os.environ["BAX_BATCH_FORCE_WORKERS"])
+        blocking = 1 if os.environ.get("BAX_BATCH_BLOCK", "0") == "1" else 0
+    batch_stats.update(workers=nw, blocking_sync=int(blocking), cpus=cpus, local_world=local_world)
+    # The interpreter's share (contiguity checks, pointer tables, the Rodrigues conversions, result tuples: ~0.37 ms per
+    # problem) is serial; the C call releases the GIL.  So the problems of a shape go through in chunks: while the
+    # native workers solve chunk i, this thread prepares chunk i + 1 and unpacks chunk i - 1 (measured on 512 problems,
+    # 12 workers: 0.45 s -> see DESIGN.md 8b).  BAX_BATCH_CHUNK=0 restores one call per shape.
+    chunk = int(os.environ.get("BAX_BATCH_CHUNK", str(max(64, 8 * nw))))
+    from concurrent.futures import ThreadPoolExecutor
+    for (Cn, C2, N, J, J3), ks_all in groups.items():
         assert Cn == C2
-        n = len(ks)
-        keep, cols = {}, {name: [] for name in ("K", "y", "s", "p3", "s3", "R", "t")}
+        keep = {}
 
         def arr(a, shape):                      # one contiguous float64 copy per distinct array object
             key = id(a)
@@ -841,67 +862,83 @@ def _ba_batch_native(idx, problems, lambda1, lambda2, n_workers, ftol=1e-4, xtol
                 b = f8(a).reshape(shape)
                 keep[key] = (a, b)
             return keep[key][1]
-        Rall = np.empty((n, Cn, 3, 3))
-        for i, k in enumerate(ks):
-            camid, K, R, t, sp2d, ss2d, sp3d, ss3d = problems[k]
-            cols["K"].append(arr(K, (Cn, 3, 3))); cols["y"].append(arr(sp2d, (Cn, N * J, 2)))
-            cols["s"].append(arr(ss2d, (Cn, N * J)))
+
+        def prep(ks):
+            n = len(ks)
+            cols = {name: [] for name in ("K", "y", "s", "p3", "s3", "R", "t")}
+            Rall = np.empty((n, Cn, 3, 3))
+            for i, k in enumerate(ks):
+                camid, K, R, t, sp2d, ss2d, sp3d, ss3d = problems[k]
+                cols["K"].append(arr(K, (Cn, 3, 3))); cols["y"].append(arr(sp2d, (Cn, N * J, 2)))
+                cols["s"].append(arr(ss2d, (Cn, N * J)))
+                if J3:
+                    cols["p3"].append(arr(sp3d, (Cn, N, J3, 3))); cols["s3"].append(arr(ss3d, (Cn, N, J3)))
+                cols["R"].append(arr(R, (Cn, 3, 3))); cols["t"].append(arr(t, (Cn, 3)))
+                Rall[i] = cols["R"][-1]
+            rvec = np.ascontiguousarray(rodrigues_inv_batch(Rall.reshape(-1, 3, 3)).reshape(n, Cn, 3))
+            ptrs = lambda xs: (C.c_void_p * n)(*[x.ctypes.data for x in xs])
+            theta = np.empty((n, 6 * Cn + 3 * N * J))
+            info = np.zeros((n, 8))
+            a = _lib.BatchArgs()
+            a.blocking_sync = blocking
+            a.n_problems, a.n_workers, a.device = n, nw, dev
+            a.C, a.N, a.J, a.J3, a.B = Cn, N, J, J3 or J, int(bones.shape[0])
+            live = [cols, rvec, theta, info, ptrs(cols["K"]), ptrs(cols["y"]), ptrs(cols["s"]), ptrs(cols["R"]),
+                    ptrs(cols["t"]), (C.c_void_p * n)(*[rvec[i].ctypes.data for i in range(n)])]
+            a.K, a.y2d, a.s2d, a.R0, a.t0, a.rvec0 = live[4:10]
             if J3:
-                cols["p3"].append(arr(sp3d, (Cn, N, J3, 3))); cols["s3"].append(arr(ss3d, (Cn, N, J3)))
-            cols["R"].append(arr(R, (Cn, 3, 3))); cols["t"].append(arr(t, (Cn, 3)))
-            Rall[i] = cols["R"][-1]
-        rvec = np.ascontiguousarray(rodrigues_inv_batch(Rall.reshape(-1, 3, 3)).reshape(n, Cn, 3))
-        ptrs = lambda xs: (C.c_void_p * n)(*[x.ctypes.data for x in xs])
-        npar = 6 * Cn + 3 * N * J
-        theta = np.empty((n, npar))
-        info = np.zeros((n, 8))
-        a = _lib.BatchArgs()
-        # worker threads spin on their scalar read-backs: one per core this rank can have.  With several ranks on one
-        # host (LOCAL_WORLD_SIZE) the cores are shared: 4 ranks x 12 spinning workers on a small host ran at a third of
-        # the single-rank rate.  Measured with 4 cores per rank: 3 workers 957, 4 workers 1163, 8 workers 1099 problems/s
-        # per rank spinning; sleeping waits (bax_set_blocking_sync) 627 / 744 / 996 — so: spin, workers = cores per rank
-        # (at least 4), sleep only when even that oversubscribes the host twice over.
-        try:
-            cpus = len(os.sched_getaffinity(0))
-        except AttributeError:
-            cpus = os.cpu_count() or 1
-        local_world = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
-        nw = max(1, min(int(n_workers), max(4, cpus // local_world)))
-        a.blocking_sync = 1 if nw * local_world > 2 * cpus else 0
-        if os.environ.get("BAX_BATCH_FORCE_WORKERS"):             # experiments: fixed worker count / wait mode
-            nw = int(os.environ["BAX_BATCH_FORCE_WORKERS"])
-            a.blocking_sync = 1 if os.environ.get("BAX_BATCH_BLOCK", "0") == "1" else 0
-        a.n_problems, a.n_workers, a.device = n, nw, dev
-        batch_stats.update(workers=nw, blocking_sync=int(a.blocking_sync), cpus=cpus, local_world=local_world)
-        a.C, a.N, a.J, a.J3, a.B = Cn, N, J, J3 or J, int(bones.shape[0])
-        pK, py, ps_, pR, pt = ptrs(cols["K"]), ptrs(cols["y"]), ptrs(cols["s"]), ptrs(cols["R"]), ptrs(cols["t"])
-        prv = (C.c_void_p * n)(*[rvec[i].ctypes.data for i in range(n)])
-        a.K, a.y2d, a.s2d, a.R0, a.t0, a.rvec0 = pK, py, ps_, pR, pt, prv
-        if J3:
-            p3, s3 = ptrs(cols["p3"]), ptrs(cols["s3"])
-            a.p3d, a.s3d = p3, s3
-        a.bones = bones.ctypes.data_as(_lib.P_i32)
-        a.lambda1, a.lambda2 = float(lambda1), float(lambda2)
-        a.ftol, a.xtol, a.gtol = float(ftol), float(xtol), float(gtol)
-        a.max_nfev = 0 if max_nfev is None else int(max_nfev)
-        a.theta_out, a.info_out = theta.ctypes.data, info.ctypes.data
-        check(L.bax_batch_solve(C.byref(a)), "bax_batch_solve")
-        Rs = rodrigues_batch(theta[:, :3 * Cn].reshape(-1, 3)).reshape(n, Cn, 3, 3)
-        for i, k in enumerate(ks):
-            st = int(info[i, 0])
-            if st == -10:
-                raise Exception(f"ba_batch: problem {k}: not enough constraint")          # reference util.py:320-321
-            if st == -11:
-                raise ValueError(f"ba_batch: problem {k}: Initial guess is outside of provided bounds")
-            th = theta[i]
-            R, t, x = Rs[i].copy(), th[3 * Cn:6 * Cn].reshape(Cn, 3, 1).copy(), th[6 * Cn:].reshape(-1, 3).copy()
-            if return_info:
-                res = dict(x=th.copy(), cost=info[i, 1], optimality=info[i, 6], nfev=int(info[i, 3]), njev=int(info[i, 4]),
-                           status=st, iterations=int(info[i, 5]), history=[], message=TERMINATION_MESSAGES[st],
-                           initial_cost=info[i, 2])
-                out[k] = (R, t, x, res)
-            else:
-                out[k] = (R, t, x)
+                live += [ptrs(cols["p3"]), ptrs(cols["s3"])]
+                a.p3d, a.s3d = live[10], live[11]
+            a.bones = bones.ctypes.data_as(_lib.P_i32)
+            a.lambda1, a.lambda2 = float(lambda1), float(lambda2)
+            a.ftol, a.xtol, a.gtol = float(ftol), float(xtol), float(gtol)
+            a.max_nfev = 0 if max_nfev is None else int(max_nfev)
+            a.theta_out, a.info_out = theta.ctypes.data, info.ctypes.data
+            return a, live, theta, info
+
+        def solve(job):                         # runs on the helper thread: the library keeps its error text per thread
+            torch.cuda.set_device(dev)
+            rc = L.bax_batch_solve(C.byref(job[0]))
+            msg = L.bax_last_error() if rc else None
+            return rc, (msg.decode() if msg else "")
+
+        def done(fut):
+            rc, msg = fut.result()
+            if rc != 0:
+                raise BaxError(f"bax_batch_solve failed ({rc}): {msg}")
+
+        def post(ks, job):
+            _, _, theta, info = job
+            Rs = rodrigues_batch(theta[:, :3 * Cn].reshape(-1, 3)).reshape(len(ks), Cn, 3, 3)
+            for i, k in enumerate(ks):
+                st = int(info[i, 0])
+                if st == -10:
+                    raise Exception(f"ba_batch: problem {k}: not enough constraint")          # reference util.py:320-321
+                if st == -11:
+                    raise ValueError(f"ba_batch: problem {k}: Initial guess is outside of provided bounds")
+                th = theta[i]
+                R, t, x = Rs[i].copy(), th[3 * Cn:6 * Cn].reshape(Cn, 3, 1).copy(), th[6 * Cn:].reshape(-1, 3).copy()
+                if return_info:
+                    res = dict(x=th.copy(), cost=info[i, 1], optimality=info[i, 6], nfev=int(info[i, 3]),
+                               njev=int(info[i, 4]), status=st, iterations=int(info[i, 5]), history=[],
+                               message=TERMINATION_MESSAGES[st], initial_cost=info[i, 2])
+                    out[k] = (R, t, x, res)
+                else:
+                    out[k] = (R, t, x)
+
+        parts = [ks_all[i:i + chunk] for i in range(0, len(ks_all), chunk)] if chunk > 0 else [ks_all]
+        with ThreadPoolExecutor(max_workers=1) as pool:
+            pending = None                       # (ks, job, future) of the chunk the native workers are on
+            for ks in parts:
+                job = prep(ks)
+                if pending is not None:
+                    done(pending[2])
+                fut = pool.submit(solve, job)
+                if pending is not None:
+                    post(pending[0], pending[1])
+                pending = (ks, job, fut)
+            done(pending[2])
+            post(pending[0], pending[1])
     return out
 
 

@@ -78,6 +78,7 @@ struct bax_handle {
   double* syrk_part;         // split-K partial tiles
   size_t syrk_part_bytes;
   double* lin_part;          // per-chunk camera sums of k_lin_fused [chunks][C][28]
+  unsigned* tickets;         // [16] arrival counters of the kernels that fold their own partials (zero between launches)
   size_t lin_part_bytes;
   double* dense_ws;          // S factor (6C x 6C), Z (B x 6C), LT (B x B), pc, w, misc
   double* coef;              // [6C + B] coefficients for back-substitution
@@ -118,6 +119,51 @@ __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
+}
+
+// ---- kernels that fold their own per-block partials (saves the k_reduce_partials / k_reduce_max launch that followed
+// them: a 4-camera problem is bound by the number of launches, not by their work).  Every block writes its partial as
+// before, then takes a ticket; the block that draws the last one sums ALL partials in the fixed order k_reduce_partials
+// uses (thread-strided over the blocks, warp tree, warps in order), so the result does not depend on which block is last.
+// The ticket returns to zero for the next launch on the stream.
+__device__ __forceinline__ bool bax_last_block(unsigned* ticket) {
+  __shared__ bool last;
+  __threadfence();                               // this block's partials are visible before its ticket is counted
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned t = atomicAdd(ticket, 1u);
+    last = (t == gridDim.x * gridDim.y - 1);
+    if (last) *ticket = 0u;
+  }
+  __syncthreads();
+  if (last) __threadfence();
+  return last;
+}
+template <int NT>
+__device__ __forceinline__ void bax_fold_sum(const double* part, int nblk, int nv, double* out, double* sm /*[32]*/) {
+  for (int v = 0; v < nv; ++v) {
+    double acc = 0.0;
+    for (int b = threadIdx.x; b < nblk; b += NT) acc += __ldcg(part + (size_t)b * nv + v);
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      double x = threadIdx.x < NT / 32 ? sm[threadIdx.x] : 0.0;
+      x = warp_sum(x);
+      if (threadIdx.x == 0) out[v] = x;
+    }
+    __syncthreads();
+  }
+}
+template <int NT>
+__device__ __forceinline__ void bax_fold_max(const double* v, int n, double* out, double* sm /*[32]*/) {
+  double mx = 0.0;
+  for (int i = threadIdx.x; i < n; i += NT) mx = fmax(mx, __ldcg(v + i));
+  for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = mx;
+  __syncthreads();
+  if (threadIdx.x == 0) { for (int w = 0; w < NT / 32; ++w) mx = fmax(mx, sm[w]); *out = mx; }
+  __syncthreads();
 }
 
 // Deterministic block sum of NV values per thread; result valid in thread 0 (array `v`).

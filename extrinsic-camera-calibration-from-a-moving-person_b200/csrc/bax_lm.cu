@@ -93,13 +93,13 @@ extern "C" int bax_cost_begin(bax_handle* h, const double* theta, void* stream) 
   if (!h || !h->campack || !theta) { bax_set_error("bax_cost_begin: bad argument / no problem"); return BAX_E_ARG; }
   cudaStream_t s = (cudaStream_t)stream;
   BAX_CUDA(cudaSetDevice(h->device));
-  BaxTimer t(h, BAX_T_COST, s, 4);
+  BaxTimer t(h, BAX_T_COST, s, 2);
   int rc = bax_launch_cam_prep(h, theta, s); if (rc) return rc;
   return bax_bone_pass1(h, theta, s);
 }
 extern "C" int bax_cost_mid(bax_handle* h, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
-  BaxTimer t(h, BAX_T_COST, s, 6);
+  BaxTimer t(h, BAX_T_COST, s, 5);
   double* out = h->buf[BAX_BUF_COST];
   int rc = bax_bone_pass2(h, h->theta, out, s); if (rc) return rc;
   int g = obs_grid(h);
@@ -460,7 +460,8 @@ __global__ void __launch_bounds__(256)
 k_gp_bone(const double* __restrict__ x, int64_t P, int J, const int32_t* __restrict__ bones,
           const int32_t* __restrict__ joint_bones, const double* __restrict__ Lbar, const double* __restrict__ rb,
           double scale, double* __restrict__ gp, const double* __restrict__ Vp,
-          double* __restrict__ part /*[grid][2]*/, double* __restrict__ pmax /*[2][grid]*/) {
+          double* __restrict__ part /*[grid][2]*/, double* __restrict__ pmax /*[2][grid]*/,
+          double* __restrict__ norm_out /*[2]*/, double* __restrict__ gmax_out /*[2]*/, unsigned* __restrict__ ticket) {
   __shared__ double sm[2 * 32];
   __shared__ double smax[16];
   double acc[2] = {0, 0}, mx = 0, mv = 0;
@@ -494,6 +495,11 @@ k_gp_bone(const double* __restrict__ x, int64_t P, int J, const int32_t* __restr
     part[2 * blockIdx.x] = acc[0]; part[2 * blockIdx.x + 1] = acc[1];
     pmax[blockIdx.x] = mx; pmax[gridDim.x + blockIdx.x] = mv;
   }
+  if (bax_last_block(ticket)) {                  // was: k_reduce_partials and two k_reduce_max after this kernel
+    bax_fold_sum<256>(part, gridDim.x, 2, norm_out, sm);
+    bax_fold_max<256>(pmax, gridDim.x, gmax_out, sm);
+    bax_fold_max<256>(pmax + gridDim.x, gridDim.x, gmax_out + 1, sm);
+  }
 }
 __global__ void k_reduce_max(const double* __restrict__ v, int n, double* __restrict__ out) {
   __shared__ double sm[32];
@@ -524,7 +530,7 @@ extern "C" int bax_linearize_begin(bax_handle* h, const double* theta, void* str
   cudaStream_t s = (cudaStream_t)stream;
   BAX_CUDA(cudaSetDevice(h->device));
   int rc = ensure_trial_buffers(h); if (rc) return rc;
-  BaxTimer t(h, BAX_T_LIN, s, 4);
+  BaxTimer t(h, BAX_T_LIN, s, 2);
   rc = bax_launch_cam_prep(h, theta, s, true); if (rc) return rc;
   return bax_bone_pass1(h, theta, s);
 }
@@ -536,7 +542,7 @@ extern "C" int bax_linearize_mid(bax_handle* h, void* stream) {
   double* lin = h->buf[BAX_BUF_LIN];
   int rc;
   {
-    BaxTimer t(h, BAX_T_LIN, s, 6);
+    BaxTimer t(h, BAX_T_LIN, s, 0);              // launches counted below
     // BAX_LINCAM: tuning knob — 5 (default) = fused camera + point kernel (0.944 -> 0.827 ms per linearisation at the
     // cfg4 shard, 0.351 -> 0.292 at cfg3, unchanged at 4 cameras); 4 = DMMA camera kernel + k_lin_pt;
     // 0..3 = DFMA camera kernel at 256x1, 128x3, 256x2, 128x4 CTAs/SM + k_lin_pt
@@ -578,6 +584,7 @@ extern "C" int bax_linearize_mid(bax_handle* h, void* stream) {
       BAX_LAUNCH_CHECK();
     }
     rc = bax_bone_pass2(h, h->theta_lin, lin + (size_t)C6 * C6 + C6, s); if (rc) return rc;
+    t.nl = (lc_variant >= 5 ? 2 : 3) + (h->B > 0 ? 1 : 0);
   }
   double* v3d = nullptr;
   if (h->Nv > 0) {
@@ -600,7 +607,7 @@ extern "C" int bax_linearize_mid(bax_handle* h, void* stream) {
 extern "C" int bax_linearize_post(bax_handle* h, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
   const int C6 = 6 * h->C;
-  BaxTimer t(h, BAX_T_LIN, s, 4);
+  BaxTimer t(h, BAX_T_LIN, s, 2);
   double* lin = h->buf[BAX_BUF_LIN];
   k_bone_finalize<<<1, 32, 0, s>>>(h->buf[BAX_BUF_BONE], lin + (size_t)C6 * C6 + C6, h->B, h->lam2, h->Lbar, h->rb);
   BAX_LAUNCH_CHECK();
@@ -609,11 +616,8 @@ extern "C" int bax_linearize_post(bax_handle* h, void* stream) {
   // scale = lam2 * 2 / Ntot ; Ntot lives on device (buf[BONE][B]); single-GPU fast path reads host N,
   // multi-GPU callers set it through bax_set_global_frames before linearising.
   double scale = h->lam2 * 2.0 / (double)h->n_frames_global;
-  k_gp_bone<<<g, 256, 0, s>>>(h->theta_lin + C6, h->P, h->J, h->bones, h->joint_bones, h->Lbar, h->rb, scale, h->gp, h->Vp, part, pmax);
-  BAX_LAUNCH_CHECK();
-  int rc = bax_reduce_partials(h, part, g, 2, h->buf[BAX_BUF_NORM], s); if (rc) return rc;
-  k_reduce_max<<<1, 256, 0, s>>>(pmax, g, h->buf[BAX_BUF_GMAX]);
-  k_reduce_max<<<1, 256, 0, s>>>(pmax + g, g, h->buf[BAX_BUF_GMAX] + 1);
+  k_gp_bone<<<g, 256, 0, s>>>(h->theta_lin + C6, h->P, h->J, h->bones, h->joint_bones, h->Lbar, h->rb, scale, h->gp, h->Vp, part, pmax,
+                              h->buf[BAX_BUF_NORM], h->buf[BAX_BUF_GMAX], h->tickets + 2);
   BAX_LAUNCH_CHECK();
   return BAX_OK;
 }

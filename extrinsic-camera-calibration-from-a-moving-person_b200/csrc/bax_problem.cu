@@ -166,7 +166,7 @@ void bax_dev_free(bax_handle* h, void* p) {
 
 static void free_problem(bax_handle* h) {
   void* ptrs[] = {(void*)h->K, h->bones, h->joint_bones, h->dhat, h->blockbase, h->campack, h->campack_lin, h->Vp, h->gp,
-                  h->Hcc, h->gc, h->Lbar, h->rb, h->lin_stage, h->Yhat, h->Gv, h->syrk_part, h->lin_part, h->dense_ws, h->coef,
+                  h->Hcc, h->gc, h->Lbar, h->rb, h->lin_stage, h->Yhat, h->Gv, h->syrk_part, h->lin_part, h->tickets, h->dense_ws, h->coef,
                   h->partials, h->saved.Vp, h->saved.gp, h->saved.lin, h->saved.Lbar, h->saved.rb, h->saved.campack_lin};
   for (void* p : ptrs) bax_dev_free(h, p);
   for (int i = 0; i < 8; ++i) { bax_dev_free(h, h->buf[i]); h->buf[i] = nullptr; }
@@ -175,7 +175,7 @@ static void free_problem(bax_handle* h) {
   h->Yhat = h->Gv = h->syrk_part = h->dense_ws = h->coef = h->partials = h->lin_stage = nullptr;
   h->saved.Vp = h->saved.gp = h->saved.lin = h->saved.Lbar = h->saved.rb = h->saved.campack_lin = nullptr; h->saved.valid = 0;
   h->syrk_part_bytes = 0;
-  h->lin_part = nullptr; h->lin_part_bytes = 0;
+  h->lin_part = nullptr; h->lin_part_bytes = 0; h->tickets = nullptr;
 }
 
 extern "C" int bax_set_blocking_sync(bax_handle* h, int on) {
@@ -290,6 +290,8 @@ extern "C" int bax_problem_set(bax_handle* h, int C, int N, int J, int J3, int B
   BAX_ALLOC(h, h->gp, sizeof(double) * 3 * h->P);
   BAX_ALLOC(h, h->Lbar, sizeof(double) * BAX_MAX_B);
   BAX_ALLOC(h, h->rb, sizeof(double) * BAX_MAX_B);
+  BAX_ALLOC(h, h->tickets, 16 * sizeof(unsigned));
+  BAX_CUDA(cudaMemsetAsync(h->tickets, 0, 16 * sizeof(unsigned), s));
   BAX_CUDA(cudaMemsetAsync(h->Lbar, 0, sizeof(double) * BAX_MAX_B, s));
   BAX_CUDA(cudaMemsetAsync(h->rb, 0, sizeof(double) * BAX_MAX_B, s));
   BAX_ALLOC(h, h->coef, sizeof(double) * (C6 + BAX_MAX_B));

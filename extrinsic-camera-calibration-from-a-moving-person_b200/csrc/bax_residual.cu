@@ -348,7 +348,8 @@ __global__ void k_var3d_residual(const double* __restrict__ campack, const doubl
 __global__ void __launch_bounds__(256)
 k_bone_len(const double* __restrict__ x, int N, int J, int B, const int32_t* __restrict__ bones,
            const double* __restrict__ bone_buf /* null in pass 1: [B] sums, [B] = count */,
-           double* __restrict__ part /*[gridDim.x][B]*/) {
+           double* __restrict__ part /*[gridDim.x][B]*/, double* __restrict__ out /*[B] (+ the frame count in pass 1)*/,
+           unsigned* __restrict__ ticket) {
   __shared__ double sm[BAX_MAX_B * 32];
   double acc[BAX_MAX_B];
 #pragma unroll
@@ -370,8 +371,11 @@ k_bone_len(const double* __restrict__ x, int N, int J, int B, const int32_t* __r
   block_sum<BAX_MAX_B>(acc, sm);
   if (threadIdx.x == 0)
     for (int b = 0; b < B; ++b) part[(size_t)blockIdx.x * B + b] = acc[b];
+  if (bax_last_block(ticket)) {                  // was: k_reduce_partials (+ k_set_scalar) after this kernel
+    bax_fold_sum<256>(part, gridDim.x, B, out, sm);
+    if (!bone_buf && threadIdx.x == 0) out[B] = (double)N;
+  }
 }
-__global__ void k_set_scalar(double* p, double v) { *p = v; }
 __global__ void k_bone_rows(const double* __restrict__ ssq, const double* __restrict__ bone_buf, int B,
                             double lam2, double* __restrict__ r_out) {
   int b = threadIdx.x;
@@ -387,10 +391,7 @@ static int bone_grid(bax_handle* h) {
 int bax_bone_pass1(bax_handle* h, const double* theta, cudaStream_t s) {
   int g = bone_grid(h);
   const double* x = theta + 6 * h->C;
-  k_bone_len<<<g, 256, 0, s>>>(x, h->N, h->J, h->B, h->bones, nullptr, h->partials);
-  BAX_LAUNCH_CHECK();
-  if (h->B > 0) { int rc = bax_reduce_partials(h, h->partials, g, h->B, h->buf[BAX_BUF_BONE], s); if (rc) return rc; }
-  k_set_scalar<<<1, 1, 0, s>>>(h->buf[BAX_BUF_BONE] + h->B, (double)h->N);
+  k_bone_len<<<g, 256, 0, s>>>(x, h->N, h->J, h->B, h->bones, nullptr, h->partials, h->buf[BAX_BUF_BONE], h->tickets + 0);
   BAX_LAUNCH_CHECK();
   return BAX_OK;
 }
@@ -400,9 +401,9 @@ int bax_bone_pass2(bax_handle* h, const double* theta, double* out, cudaStream_t
   int g = bone_grid(h);
   const double* x = theta + 6 * h->C;
   double* part = h->partials + (size_t)(1 << 21);     // second half: pass-1 partials may still be live
-  k_bone_len<<<g, 256, 0, s>>>(x, h->N, h->J, h->B, h->bones, h->buf[BAX_BUF_BONE], part);
+  k_bone_len<<<g, 256, 0, s>>>(x, h->N, h->J, h->B, h->bones, h->buf[BAX_BUF_BONE], part, out, h->tickets + 1);
   BAX_LAUNCH_CHECK();
-  return bax_reduce_partials(h, part, g, h->B, out, s);
+  return BAX_OK;
 }
 
 // ------------------------------------------------------------------ API

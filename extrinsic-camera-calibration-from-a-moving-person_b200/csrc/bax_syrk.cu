@@ -118,6 +118,72 @@ k_syrk_reduce(const double* __restrict__ part, int rows, int ntiles, int nsplit,
   }
 }
 
+__device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+               : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
+
+// ------------------------------------------------------------------ up to 64 rows on the FP64 tensor pipe
+// The reference's own scenes have 3-5 cameras: 6C + B + 1 = 31..43 rows (and 3C + 1 = 10..16 for the orientation rows).
+// k_syrk above computes a full 64 x 64 tile for them (4096 products per column where 37 rows need 703) on the DFMA pipe
+// and cuts K into ~200 CTAs of 256 threads that fill the whole GPU for a 20-30 us kernel — which is also what keeps the
+// streams of a sweep over many small problems (bax_batch_solve) from overlapping.  Here one WARP is a split-K unit: it
+// keeps the NT8 (NT8 + 1) / 2 lower m8n8 accumulator tiles of the whole product in registers, reads its operand
+// fragments X[8 i + g][k + tig] straight from global memory (four lanes share a 32-byte sector, four consecutive steps a
+// 128-byte line held in L1; Yhat of such a problem lives in L2) one 16-column step ahead, and issues NT8 (NT8 + 1) / 2
+// DMMA per 4 columns.  Partials go out in the 64 x 64 layout k_syrk_reduce already sums in a fixed order.
+template <int NT8>
+__device__ __forceinline__ void ssm_load(double (&f)[4][NT8], const double* const (&rp)[NT8], const bool (&ok)[NT8], int64_t k) {
+#pragma unroll
+  for (int s4 = 0; s4 < 4; ++s4)
+#pragma unroll
+    for (int i = 0; i < NT8; ++i) f[s4][i] = ok[i] ? rp[i][k + 4 * s4] : 0.0;
+}
+template <int NT8>
+__device__ __forceinline__ void ssm_mma(double (&acc)[NT8 * (NT8 + 1) / 2][2], const double (&f)[4][NT8]) {
+#pragma unroll
+  for (int s4 = 0; s4 < 4; ++s4) {
+    int t = 0;
+#pragma unroll
+    for (int i = 0; i < NT8; ++i)
+#pragma unroll
+      for (int j = 0; j <= i; ++j) { dmma884(acc[t], f[s4][i], f[s4][j]); ++t; }
+  }
+}
+template <int NT8>
+__global__ void __launch_bounds__(128)
+k_syrk_small(const double* __restrict__ X, int rows, int64_t ldx, int64_t kw /*columns per warp, multiple of 32*/, int64_t Kpad,
+             int nunits, double* __restrict__ part /*[nunits][64 x 64]*/) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, tig = lane & 3;
+  const int unit = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (unit >= nunits) return;
+  const int64_t kbeg = (int64_t)unit * kw;
+  int64_t kend = kbeg + kw; if (kend > Kpad) kend = Kpad;
+  const double* rp[NT8]; bool ok[NT8];
+#pragma unroll
+  for (int i = 0; i < NT8; ++i) { ok[i] = 8 * i + g < rows; rp[i] = X + (size_t)(ok[i] ? 8 * i + g : 0) * ldx + tig; }
+  double acc[NT8 * (NT8 + 1) / 2][2];
+#pragma unroll
+  for (int t = 0; t < NT8 * (NT8 + 1) / 2; ++t) { acc[t][0] = 0.0; acc[t][1] = 0.0; }
+  double fa[4][NT8], fb[4][NT8];
+  ssm_load<NT8>(fa, rp, ok, kbeg);
+  for (int64_t k = kbeg; k < kend; k += 32) {    // kw and Kpad are multiples of 32: two 16-column steps per round
+    ssm_load<NT8>(fb, rp, ok, k + 16);
+    ssm_mma<NT8>(acc, fa);
+    if (k + 32 < kend) ssm_load<NT8>(fa, rp, ok, k + 32);
+    ssm_mma<NT8>(acc, fb);
+  }
+  double* o = part + (size_t)unit * (ST * ST);
+  int t = 0;
+#pragma unroll
+  for (int i = 0; i < NT8; ++i)
+#pragma unroll
+    for (int j = 0; j <= i; ++j) {
+      *reinterpret_cast<double2*>(o + (8 * i + g) * ST + 8 * j + 2 * tig) = make_double2(acc[t][0], acc[t][1]);
+      ++t;
+    }
+}
+
 // ------------------------------------------------------------------ 96 x 96 tiles on the FP64 tensor pipe (DMMA)
 // Measured on this B200 (tools/micro/fp64_peak.cu): mma.sync.m8n8k4.f64 sustains 37.1 TFLOP/s, the DFMA vector pipe
 // 34 TFLOP/s and only with >= 16 resident warps; a 6 x 6 DFMA register tile reached 61 % pipe utilisation.  Here a
@@ -126,34 +192,33 @@ k_syrk_reduce(const double* __restrict__ part, int rows, int ntiles, int nsplit,
 // X[row0 + (lane >> 2)][k0 + (lane & 3)]: with a row stride of 20 doubles the 32 lanes hit 32 distinct 8-byte banks
 // slots twice (two wavefronts, the minimum for 256 bytes).  3-stage cp.async pipeline of 16 K columns, 2 CTAs / SM.
 #define T9 96
+#ifndef KC9
 #define KC9 16
-#define LD9 20
 #define ST9 3
+#endif
+#define LD9 (KC9 + 4)
 #define STAGE9 (2 * T9 * LD9)
 
 __device__ __forceinline__ void load_tile96(double* dst, const double* __restrict__ X, int row0, int rows, int64_t ldx, int64_t k0) {
-  const int t = threadIdx.x;           // 96 rows x 16 columns = 768 16-byte words; 128 threads x 6
+  const int t = threadIdx.x;           // 96 rows x KC9 columns = 48 KC9 16-byte words; 128 threads x (3 KC9 / 8)
 #pragma unroll
-  for (int i = 0; i < 6; ++i) {
+  for (int i = 0; i < 3 * KC9 / 8; ++i) {
     int w = t + 128 * i;
-    int r = w >> 3, c2 = (w & 7) * 2;
+    int r = w / (KC9 / 2), c2 = (w % (KC9 / 2)) * 2;
     bool ok = (row0 + r) < rows;
     const double* src = X + (size_t)(ok ? row0 + r : 0) * ldx + k0 + c2;
     cp_async16(dst + r * LD9 + c2, src, ok);
   }
 }
 
-__device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
-               : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
-}
 
 // Trailing rows ("extras": the bone-length and right-hand-side rows of Yhat, the residual row of the orientation
 // Jacobian) ride along in the diagonal tiles: every tile row of a diagonal tile also forms its 8 x 16 piece of the panel
 // X[tile rows] . X[extras]^T, and tile 0 the 16 x 16 corner  X[extras] . X[extras]^T.  The extras cost one more 16-row
 // slab per stage and no extra pass over X.
 #define NE9 16
-#define STAGE9E (STAGE9 + NE9 * LD9)
+#define STAGE9E STAGE9                           // the extras slab of a diagonal tile lies where an off-diagonal tile keeps B
+#define EOFF9 (T9 * LD9)
 #define EP9 ((T9 + NE9) * NE9)                   // doubles of one panel partial: [96 panel rows + 16 corner rows][16]
 
 // Work of a DIAGONAL tile.  Only its lower triangle is read back, so computing 48 x 48 quadrants there wastes a third of
@@ -291,10 +356,14 @@ k_syrk96(const double* __restrict__ X, int rows, int ne, int64_t ldx, int nt, in
     double* d = sm + st * STAGE9E;
     load_tile96(d, X, bi * T9, rows, ldx, k0);
     if (!diag) load_tile96(d + T9 * LD9, X, bj * T9, rows, ldx, k0);
-    else if (with_e) {                           // 16 rows x 16 columns = 128 16-byte words, one per thread
-      const int r = threadIdx.x >> 3, c2 = (threadIdx.x & 7) * 2;
-      const bool ok = r < ne;
-      cp_async16(d + 2 * T9 * LD9 + r * LD9 + c2, X + (size_t)(ok ? rows + r : 0) * ldx + k0 + c2, ok);
+    else if (with_e) {                           // 16 rows x KC9 columns = 8 KC9 16-byte words
+#pragma unroll
+      for (int i = 0; i < KC9 / 16; ++i) {
+        const int w = threadIdx.x + 128 * i;
+        const int r = w / (KC9 / 2), c2 = (w % (KC9 / 2)) * 2;
+        const bool ok = r < ne;
+        cp_async16(d + EOFF9 + r * LD9 + c2, X + (size_t)(ok ? rows + r : 0) * ldx + k0 + c2, ok);
+      }
     }
   };
 #pragma unroll
@@ -327,7 +396,7 @@ k_syrk96(const double* __restrict__ X, int rows, int ne, int64_t ldx, int nt, in
           for (int j = 0; j < 6; ++j) dmma884(acc[6 * i + j], a[i], bb[j]);
       }
     } else {
-      const double* Es = As + 2 * T9 * LD9;
+      const double* Es = As + EOFF9;
       switch (warp) {                            // uniform per warp
         case 0: dg_chunk_any<0>(acc, As, Es, with_e, corner, g, tig); break;
         case 1: dg_chunk_any<1>(acc, As, Es, with_e, corner, g, tig); break;
@@ -456,6 +525,28 @@ int bax_syrk_aug(bax_handle* h, const double* X, int rows, int ne, int64_t K, in
     return BAX_OK;
   }
   rows += ne;                                    // small systems: one 64 x 64 tile covers everything
+  static const int small_mma = getenv("BAX_SYRK_SMALL") ? atoi(getenv("BAX_SYRK_SMALL")) : 1;   // 0: the DFMA tile kernel below
+  if (small_mma && rows <= 48) {                 // 7 and 8 tile rows do not fit the register file with a double-buffered operand set
+    const int nt8 = (rows + 7) / 8;
+    // one warp per split-K unit, at least 128 columns each, at most 8 warps per SM
+    int64_t kw = (Kpad + 8 * (int64_t)h->sm_count - 1) / (8 * (int64_t)h->sm_count);
+    kw = ((kw + KC - 1) / KC) * KC;
+    if (kw < 128) kw = 128;
+    const int nunits = (int)((Kpad + kw - 1) / kw);
+    int rc = ensure_part(h, sizeof(double) * (size_t)nunits * ST * ST); if (rc) return rc;
+    BaxTimer t(h, BAX_T_SYRK, s, 2);
+    const int nb = (nunits + 3) / 4;
+    switch (nt8) {
+      case 1: case 2: k_syrk_small<2><<<nb, 128, 0, s>>>(X, rows, ldx, kw, Kpad, nunits, h->syrk_part); break;
+      case 3: case 4: k_syrk_small<4><<<nb, 128, 0, s>>>(X, rows, ldx, kw, Kpad, nunits, h->syrk_part); break;
+      case 5: k_syrk_small<5><<<nb, 128, 0, s>>>(X, rows, ldx, kw, Kpad, nunits, h->syrk_part); break;
+      default: k_syrk_small<6><<<nb, 128, 0, s>>>(X, rows, ldx, kw, Kpad, nunits, h->syrk_part); break;
+    }
+    BAX_LAUNCH_CHECK();
+    k_syrk_reduce<<<(rows * rows + 31) / 32, 256, 0, s>>>(h->syrk_part, rows, 1, nunits, out, ldo);
+    BAX_LAUNCH_CHECK();
+    return BAX_OK;
+  }
   const int nt = (rows + ST - 1) / ST;
   const int ntiles = nt * (nt + 1) / 2;
   int64_t nsplit = (4 * (int64_t)h->sm_count + ntiles - 1) / ntiles;

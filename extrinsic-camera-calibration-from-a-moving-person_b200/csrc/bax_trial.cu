@@ -111,7 +111,8 @@ __global__ void __launch_bounds__(128)
 k_backsub(const double* __restrict__ s, int64_t P, int C, int J, int B, const int32_t* __restrict__ joint_bones,
           const double* __restrict__ Vp, const double* __restrict__ gp, double alpha,
           double* __restrict__ Yhat, int64_t ldy, const double* __restrict__ coef,
-          double* __restrict__ step_pts, double* __restrict__ part) {
+          double* __restrict__ step_pts, double* __restrict__ part, double* __restrict__ sums_out /*[3]*/,
+          unsigned* __restrict__ ticket) {
   extern __shared__ double sm_all[];             // coef [6C+B] then reduction scratch [3*32]
   double* cf = sm_all;
   double* red = sm_all + ((6 * C + B + 1) & ~1);
@@ -156,6 +157,7 @@ k_backsub(const double* __restrict__ s, int64_t P, int C, int J, int B, const in
   }
   block_sum<3>(acc, red);
   if (threadIdx.x == 0) { part[3 * blockIdx.x] = acc[0]; part[3 * blockIdx.x + 1] = acc[1]; part[3 * blockIdx.x + 2] = acc[2]; }
+  if (bax_last_block(ticket)) bax_fold_sum<128>(part, gridDim.x, 3, sums_out, red);   // was: k_reduce_partials after this kernel
 }
 
 // out[i] = sum_k Yhat[i][k] * Yhat[last][k], split over K chunks (deterministic two-stage sum)
@@ -217,7 +219,7 @@ extern "C" int bax_trial_mid(bax_handle* h, double* step, int need_phi_prime, vo
   const int C = h->C, C6 = 6 * C, B = h->B;
   int rc = bax_dense_solve1(h, s); if (rc) return rc;
   {
-    BaxTimer t(h, BAX_T_BACKSUB, s, 3);
+    BaxTimer t(h, BAX_T_BACKSUB, s, 2);
     // camera part of the step, theta order (rvecs first, then tvecs): done by a tiny copy kernel in bax_dense.cu
     rc = bax_scatter_cam_step(h, step, s); if (rc) return rc;
     int nb = (int)((h->P + 127) / 128);
@@ -225,10 +227,9 @@ extern "C" int bax_trial_mid(bax_handle* h, double* step, int need_phi_prime, vo
     double* part = h->partials;
     if ((size_t)nb * 3 > (1u << 21)) { bax_set_error("partials overflow in backsub"); return BAX_E_STATE; }
     k_backsub<<<nb, 128, sm, s>>>(h->s2d, h->P, C, h->J, B, h->joint_bones, h->Vp, h->gp, h->alpha, h->Yhat, h->ldy,
-                                  h->coef, step + C6, part);
+                                  h->coef, step + C6, part, h->buf[BAX_BUF_RHS2] + C6 + B, h->tickets + 3);
     BAX_LAUNCH_CHECK();
     double* rhs2 = h->buf[BAX_BUF_RHS2];
-    rc = bax_reduce_partials(h, part, nb, 3, rhs2 + C6 + B, s); if (rc) return rc;
     if (need_phi_prime) {
       rc = launch_phi_rhs(h, s); if (rc) return rc;
     } else {
