@@ -32,12 +32,12 @@ __device__ void chol_blocked(double* __restrict__ A, int n, int ld, double* Dg, 
         Pn[r * LDS_ + c] = A[(size_t)(base + r) * ld + j0 + c];
       }
       __syncthreads();
-      for (int r = tid; r < m; r += nt) {        // L21 = A21 L11^-T, one row per thread
-        double* row = Pn + r * LDS_;
+      for (int r = tid; r < m; r += nt) {        // L21 = A21 L11^-T, one row per thread (1 / L_tt from the factorisation,
+        double* row = Pn + r * LDS_;             // as in the cooperative kernel's trsm32_cta: no FP64 division per entry)
         for (int t = 0; t < nb; ++t) {
           double v = row[t];
           for (int u = 0; u < t; ++u) v -= row[u] * Dg[t * LDS_ + u];
-          row[t] = v / Dg[t * LDS_ + t];
+          row[t] = v * rinv_s[t];
         }
       }
       __syncthreads();
@@ -96,33 +96,48 @@ __device__ void trsv_blocked(const double* __restrict__ A, int n, int ld, double
       double acc = lane < nb ? x[j0 + lane] : 0.0;
       const double rinv = lane < nb ? 1.0 / Dg[lane * LDS_ + lane] : 0.0;
       double mine = 0.0;
+      // selects instead of branches, fixed trip count (steps k >= nb see acc = rinv = 0 and change nothing)
       if (!transpose) {
-        for (int k = 0; k < nb; ++k) {
+#pragma unroll
+        for (int k = 0; k < NBK; ++k) {
           const double xk = __shfl_sync(0xffffffffu, acc, k) * __shfl_sync(0xffffffffu, rinv, k);
-          if (lane == k) mine = xk;
-          if (lane > k && lane < nb) acc -= Dg[lane * LDS_ + k] * xk;
+          mine = lane == k ? xk : mine;
+          const double l = (lane > k && lane < nb) ? Dg[lane * LDS_ + k] : 0.0;
+          acc -= l * xk;
         }
       } else {
-        for (int k = nb - 1; k >= 0; --k) {
+#pragma unroll
+        for (int k = NBK - 1; k >= 0; --k) {
           const double xk = __shfl_sync(0xffffffffu, acc, k) * __shfl_sync(0xffffffffu, rinv, k);
-          if (lane == k) mine = xk;
-          if (lane < k) acc -= Dg[k * LDS_ + lane] * xk;
+          mine = lane == k ? xk : mine;
+          const double l = (lane < k && k < nb) ? Dg[k * LDS_ + lane] : 0.0;
+          acc -= l * xk;
         }
       }
       if (lane < nb) x[j0 + lane] = mine;
     }
     __syncthreads();
+    // the NBK loads of an unknown are issued together (a run-time trip count left them one L2 round trip each:
+    // 166k of the cooperative solve's 714k cycles at 384 unknowns went into this loop)
     if (!transpose) {
       for (int i = j0 + nb + tid; i < n; i += nt) {
-        double v = x[i];
         const double* row = A + (size_t)i * ld + j0;
-        for (int t = 0; t < nb; ++t) v -= row[t] * x[j0 + t];
+        double a[NBK];
+#pragma unroll
+        for (int t = 0; t < NBK; ++t) a[t] = t < nb ? row[t] : 0.0;
+        double v = x[i];
+#pragma unroll
+        for (int t = 0; t < NBK; ++t) if (t < nb) v -= a[t] * x[j0 + t];
         x[i] = v;
       }
     } else {
       for (int i = tid; i < j0; i += nt) {
+        double a[NBK];
+#pragma unroll
+        for (int t = 0; t < NBK; ++t) a[t] = t < nb ? A[(size_t)(j0 + t) * ld + i] : 0.0;
         double v = x[i];
-        for (int t = 0; t < nb; ++t) v -= A[(size_t)(j0 + t) * ld + i] * x[j0 + t];
+#pragma unroll
+        for (int t = 0; t < NBK; ++t) if (t < nb) v -= a[t] * x[j0 + t];
         x[i] = v;
       }
     }
@@ -296,14 +311,18 @@ __device__ void trsm32_cta(double* Pn, const double* Dg, const double* rinv) {
   double e[4];
 #pragma unroll
   for (int q = 0; q < 4; ++q) e[q] = Pn[r * LDS_ + cg + 8 * q];
+  // Branch-free and fully unrolled: written with `if (t == u) .. else if (t > u) ..` and a run-time u, the eight column
+  // owners of a warp took different paths through four reconvergence regions per step and a step cost ~400 cycles
+  // (172k of the cooperative solve's 714k cycles at 384 unknowns); as selects it is one shuffle and four FMAs.
+#pragma unroll
   for (int u = 0; u < NBK; ++u) {
-    double x = sel4(e, u >> 3) * rinv[u];
+    double x = e[u >> 3] * rinv[u];
     x = __shfl_sync(0xffffffffu, x, (lane & ~7) | (u & 7));      // from the owner of column u in this row
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const int t = cg + 8 * q;
-      if (t == u) e[q] = x;
-      else if (t > u) e[q] = fma(-x, Dg[t * LDS_ + u], e[q]);
+      const double upd = fma(-x, Dg[t * LDS_ + u], e[q]);
+      e[q] = t == u ? x : (t > u ? upd : e[q]);
     }
   }
 #pragma unroll
@@ -405,8 +424,10 @@ k_dense_solve1_coop(const double* __restrict__ schur, int R, const double* __res
         Pn[r * LDS_ + c] = (r < nr && c < nb) ? src[c] : 0.0;
       }
       __syncthreads();
+      PROF(8)
       trsm32_cta(Pn, Dg, rinv);
       __syncthreads();
+      PROF(9)
       for (int idx = tid; idx < nr * NBK; idx += nt) {
         const int r = idx >> 5, c = idx & 31;
         double* dst = rb + r < m ? A + (size_t)(base + rb + r) * n + j0 : d.qc + j0;
@@ -481,8 +502,8 @@ k_dense_solve1_coop(const double* __restrict__ schur, int R, const double* __res
   if (tid < B) { d.w[tid] = sh[tid]; coef[n + tid] = sh[tid]; }
   PROF(7)
   if (prof && tid == 0)
-    printf("dense coop cycles: init %lld gridsync %lld assemble %lld diagload %lld factor %lld panel %lld trailing %lld solve %lld\n",
-           tp[0], tp[1], tp[2], tp[3], tp[4], tp[5], tp[6], tp[7]);
+    printf("dense coop cycles: init %lld gridsync %lld assemble %lld diagload %lld factor %lld panel load %lld trsm %lld store %lld trailing %lld solve %lld\n",
+           tp[0], tp[1], tp[2], tp[3], tp[4], tp[8], tp[9], tp[5], tp[6], tp[7]);
 #undef PROF
 }
 
