@@ -9,7 +9,7 @@ namespace cg = cooperative_groups;
 
 // In-place lower Cholesky of A (n x n, row-major, leading dimension ld, global/L2 resident).
 // Dg: [32][33] shared, Pn: [(n-32)][33] shared.  Right-looking, 32-wide panels, 4x4 register tiles.
-__device__ void chol32_warp(double* Dg, double* rinv);
+__device__ __noinline__ void chol32_warp(double* Dg, double* rinv);
 __device__ void chol_blocked(double* __restrict__ A, int n, int ld, double* Dg, double* Pn) {
   __shared__ double rinv_s[NBK];
   const int tid = threadIdx.x, nt = blockDim.x;
@@ -162,6 +162,30 @@ __device__ void small_chol(double* T, int B) {     // in place lower, row-major 
       for (int j = k + 1; j <= i; ++j) T[i * BAX_MAX_B + j] -= T[i * BAX_MAX_B + k] * T[j * BAX_MAX_B + k];
   }
 }
+// The same factorisation through the warp routine (T padded with the identity into a 32 x 32 block): one thread
+// working through shared memory took 45k cycles for B = 12 — a third of the whole reduced solve of a 4-camera problem.
+// Leaves 1 / L_aa in rinvT[BAX_MAX_B].  Ends with a CTA barrier.
+__device__ void small_chol_warp(double* T, int B, double* Dg, double* rinv32, double* rinvT) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  for (int idx = tid; idx < NBK * NBK; idx += nt) {
+    const int r = idx >> 5, c = idx & 31;
+    Dg[r * LDS_ + c] = (r < B && c <= r) ? T[r * BAX_MAX_B + c] : (r == c ? 1.0 : 0.0);
+  }
+  __syncthreads();
+  chol32_warp(Dg, rinv32);
+  for (int idx = tid; idx < BAX_MAX_B * BAX_MAX_B; idx += nt) {
+    const int r = idx / BAX_MAX_B, c = idx % BAX_MAX_B;
+    if (r < B && c <= r) T[idx] = Dg[r * LDS_ + c];
+  }
+  if (tid < BAX_MAX_B) rinvT[tid] = tid < B ? rinv32[tid] : 1.0;
+  __syncthreads();
+}
+__device__ void small_fwd_r(const double* L, const double* ri, int B, double* v) {       // reciprocals instead of divisions
+  for (int a = 0; a < B; ++a) { double s = v[a]; for (int b = 0; b < a; ++b) s -= L[a * BAX_MAX_B + b] * v[b]; v[a] = s * ri[a]; }
+}
+__device__ void small_bwd_r(const double* L, const double* ri, int B, double* v) {
+  for (int a = B - 1; a >= 0; --a) { double s = v[a]; for (int b = a + 1; b < B; ++b) s -= L[b * BAX_MAX_B + a] * v[b]; v[a] = s * ri[a]; }
+}
 __device__ void small_fwd(const double* L, int B, double* v) {
   for (int a = 0; a < B; ++a) { double s = v[a]; for (int b = 0; b < a; ++b) s -= L[a * BAX_MAX_B + b] * v[b]; v[a] = s / L[a * BAX_MAX_B + a]; }
 }
@@ -169,7 +193,10 @@ __device__ void small_bwd(const double* L, int B, double* v) {
   for (int a = B - 1; a >= 0; --a) { double s = v[a]; for (int b = a + 1; b < B; ++b) s -= L[b * BAX_MAX_B + a] * v[b]; v[a] = s / L[a * BAX_MAX_B + a]; }
 }
 
-__global__ void __launch_bounds__(DN_THREADS)
+// NT = 1024 caps the kernel at 64 registers, which spills the warp factorisation's 32-double row; small systems (little
+// to share out anyway) run the NT = 256 instance.
+template <int NT>
+__global__ void __launch_bounds__(NT)
 k_dense_solve1(const double* __restrict__ schur, int R, const double* __restrict__ lin, int n, int B, double alpha,
                double* __restrict__ ws, double* __restrict__ coef) {
   extern __shared__ double smem[];
@@ -188,7 +215,9 @@ k_dense_solve1(const double* __restrict__ schur, int R, const double* __restrict
   }
   if (tid < BAX_MAX_B) sh[tid] = tid < B ? schur[(size_t)(n + tid) * R + n + B] : 0.0;
   __syncthreads();
-  if (tid == 0) { small_chol(sLT, B); small_fwd(sLT, B, sh); }
+  __shared__ double s_rinv32[NBK], s_trinv[BAX_MAX_B];
+  small_chol_warp(sLT, B, Dg, s_rinv32, s_trinv);
+  if (tid == 0) small_fwd_r(sLT, s_trinv, B, sh);
   __syncthreads();
   for (int i = tid; i < BAX_MAX_B * BAX_MAX_B; i += nt) d.LT[i] = sLT[i];
   if (tid < BAX_MAX_B) d.hz[tid] = sh[tid];
@@ -202,7 +231,7 @@ k_dense_solve1(const double* __restrict__ schur, int R, const double* __restrict
       double s = z[a];
 #pragma unroll
       for (int b = 0; b < BAX_MAX_B; ++b) if (b < a) s -= sLT[a * BAX_MAX_B + b] * z[b];
-      z[a] = s / sLT[a * BAX_MAX_B + a];
+      z[a] = s * s_trinv[a];
     }
 #pragma unroll
     for (int a = 0; a < BAX_MAX_B; ++a) if (a < B) d.Z[(size_t)a * n + i] = z[a];
@@ -233,7 +262,7 @@ k_dense_solve1(const double* __restrict__ schur, int R, const double* __restrict
     sh[tid] = hv;
   }
   __syncthreads();
-  if (tid == 0) { small_fwd(sLT, B, sh); small_bwd(sLT, B, sh); }
+  if (tid == 0) { small_fwd_r(sLT, s_trinv, B, sh); small_bwd_r(sLT, s_trinv, B, sh); }
   __syncthreads();
   if (tid < B) { d.w[tid] = sh[tid]; coef[n + tid] = sh[tid]; }
 }
@@ -281,7 +310,10 @@ __device__ void chol32_cta(double* Dg, double* rinv, double* colbuf /*[2][32]*/)
 // entries travel by shuffle, no barrier and no shared-memory round trip per column (the 256-thread version above spends
 // ~720 cycles per column on them: 23k cycles per block, a third of the cooperative solve at 384 unknowns).  Same
 // arithmetic per entry as chol32_cta (bitwise).  Ends with a CTA barrier.
-__device__ void chol32_warp(double* Dg, double* rinv) {
+// (noinline: one copy per kernel.  The fully unrolled body is ~50 KB of code; a second inlined copy — the B x B system of
+// the bone-length rows goes through it too — slowed every call from 8.6k to 11.2k cycles.  A rolled column loop that
+// shifts the row by one register per column keeps the code at 4 KB but issues twice the shuffles: 15.3k cycles.)
+__device__ __noinline__ void chol32_warp(double* Dg, double* rinv) {
   if (threadIdx.x < 32) {
     const int lane = threadIdx.x;
     double e[NBK];
@@ -356,7 +388,9 @@ k_dense_solve1_coop(const double* __restrict__ schur, int R, const double* __res
   }
   if (tid < BAX_MAX_B) sh[tid] = tid < B ? schur[(size_t)(n + tid) * R + n + B] : 0.0;
   __syncthreads();
-  if (tid == 0) { small_chol(sLT, B); small_fwd(sLT, B, sh); }
+  __shared__ double s_trinv[BAX_MAX_B];
+  small_chol_warp(sLT, B, Dg, rinv, s_trinv);
+  if (tid == 0) small_fwd_r(sLT, s_trinv, B, sh);
   __syncthreads();
   if (cta == 0) {
     for (int i = tid; i < BAX_MAX_B * BAX_MAX_B; i += nt) d.LT[i] = sLT[i];
@@ -372,7 +406,7 @@ k_dense_solve1_coop(const double* __restrict__ schur, int R, const double* __res
       double v = z[a];
 #pragma unroll
       for (int b = 0; b < BAX_MAX_B; ++b) if (b < a) v -= sLT[a * BAX_MAX_B + b] * z[b];
-      z[a] = v / sLT[a * BAX_MAX_B + a];
+      z[a] = v * s_trinv[a];
     }
 #pragma unroll
     for (int a = 0; a < BAX_MAX_B; ++a) if (a < B) d.Z[(size_t)a * n + i] = z[a];
@@ -497,7 +531,7 @@ k_dense_solve1_coop(const double* __restrict__ schur, int R, const double* __res
     sh[tid] = hv;
   }
   __syncthreads();
-  if (tid == 0) { small_fwd(sLT, B, sh); small_bwd(sLT, B, sh); }
+  if (tid == 0) { small_fwd_r(sLT, s_trinv, B, sh); small_bwd_r(sLT, s_trinv, B, sh); }
   __syncthreads();
   if (tid < B) { d.w[tid] = sh[tid]; coef[n + tid] = sh[tid]; }
   PROF(7)
@@ -603,10 +637,16 @@ int bax_dense_solve1(bax_handle* h, cudaStream_t s) {
   }
   size_t sm = dense_smem(n);
   if (sm > 227 * 1024) { bax_set_error("reduced camera system of %d unknowns exceeds the single-CTA solver", n); return BAX_E_ARG; }
-  BAX_CUDA(cudaFuncSetAttribute(k_dense_solve1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   BaxTimer t(h, BAX_T_DENSE, s, 1);
-  k_dense_solve1<<<1, DN_THREADS, sm, s>>>(h->buf[BAX_BUF_SCHUR], h->R, h->buf[BAX_BUF_LIN], n, h->B, h->alpha,
-                                           h->dense_ws, h->coef);
+  static const int small_nt = getenv("BAX_DENSE_SMALL_NT") ? atoi(getenv("BAX_DENSE_SMALL_NT")) : 256;   // tuning aid: 1024 = one instance for all
+  if (n <= 96 && small_nt == 256) {
+    BAX_CUDA(cudaFuncSetAttribute(k_dense_solve1<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    k_dense_solve1<256><<<1, 256, sm, s>>>(h->buf[BAX_BUF_SCHUR], h->R, h->buf[BAX_BUF_LIN], n, h->B, h->alpha, h->dense_ws, h->coef);
+  } else {
+    BAX_CUDA(cudaFuncSetAttribute(k_dense_solve1<DN_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    k_dense_solve1<DN_THREADS><<<1, DN_THREADS, sm, s>>>(h->buf[BAX_BUF_SCHUR], h->R, h->buf[BAX_BUF_LIN], n, h->B, h->alpha,
+                                                         h->dense_ws, h->coef);
+  }
   BAX_LAUNCH_CHECK();
   return BAX_OK;
 }
