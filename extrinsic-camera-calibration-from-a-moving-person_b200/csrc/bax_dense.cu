@@ -198,7 +198,7 @@ __device__ void small_bwd(const double* L, int B, double* v) {
 template <int NT>
 __global__ void __launch_bounds__(NT)
 k_dense_solve1(const double* __restrict__ schur, int R, const double* __restrict__ lin, int n, int B, double alpha,
-               double* __restrict__ ws, double* __restrict__ coef) {
+               double* __restrict__ ws, double* __restrict__ coef, double* __restrict__ step /*camera part, theta order*/) {
   extern __shared__ double smem[];
   double* Dg = smem;                        // 32*33
   double* xs = Dg + NBK * LDS_;             // n
@@ -254,7 +254,11 @@ k_dense_solve1(const double* __restrict__ schur, int R, const double* __restrict
   chol_blocked(d.Sf, n, n, Dg, Pn);
   trsv_blocked(d.Sf, n, n, xs, Dg, false);
   trsv_blocked(d.Sf, n, n, xs, Dg, true);
-  for (int i = tid; i < n; i += nt) { d.pc[i] = xs[i]; coef[i] = xs[i]; }
+  for (int i = tid; i < n; i += nt) {           // internal order 6c + {rvec, t} -> theta order (all rvecs, then all tvecs)
+    d.pc[i] = xs[i]; coef[i] = xs[i];
+    const int c = i / 6, a = i % 6, C = n / 6;
+    step[a < 3 ? 3 * c + a : 3 * C + 3 * c + (a - 3)] = xs[i];
+  }
   // 5. w = T^-1 (h0 - G^T pc)
   if (tid < B) {
     double hv = schur[(size_t)(n + tid) * R + n + B];
@@ -363,7 +367,7 @@ __device__ void trsm32_cta(double* Pn, const double* Dg, const double* rinv) {
 
 __global__ void __launch_bounds__(CG_THREADS)
 k_dense_solve1_coop(const double* __restrict__ schur, int R, const double* __restrict__ lin, int n, int B, double alpha,
-                    double* __restrict__ ws, double* __restrict__ coef, int prof, int chol_warp) {
+                    double* __restrict__ ws, double* __restrict__ coef, int prof, int chol_warp, double* __restrict__ step) {
   long long tp[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; long long tc = clock64();
 #define PROF(i) { long long t_ = clock64(); tp[i] += t_ - tc; tc = t_; }
   cg::grid_group grid = cg::this_grid();
@@ -522,7 +526,11 @@ k_dense_solve1_coop(const double* __restrict__ schur, int R, const double* __res
   for (int i = tid; i < n; i += nt) xs[i] = d.qc[i];
   __syncthreads();
   trsv_blocked(d.Sf, n, n, xs, Dg, true);       // the forward substitution happened during the factorisation
-  for (int i = tid; i < n; i += nt) { d.pc[i] = xs[i]; coef[i] = xs[i]; }
+  for (int i = tid; i < n; i += nt) {
+    d.pc[i] = xs[i]; coef[i] = xs[i];
+    const int c = i / 6, a = i % 6, C = n / 6;
+    step[a < 3 ? 3 * c + a : 3 * C + 3 * c + (a - 3)] = xs[i];
+  }
   // 6. w = T^-1 (h0 - G^T pc)
   __syncthreads();
   if (tid < B) {
@@ -615,7 +623,7 @@ static size_t dense_smem(int n) {
   return (d + pn) * sizeof(double);
 }
 
-int bax_dense_solve1(bax_handle* h, cudaStream_t s) {
+int bax_dense_solve1(bax_handle* h, double* step, cudaStream_t s) {   // also writes the camera part of the step (theta order)
   const int n = 6 * h->C;
   if (n > NBK && h->dense_coop) {
     const int mb = (n + NBK - 1) / NBK - 1;
@@ -630,7 +638,7 @@ int bax_dense_solve1(bax_handle* h, cudaStream_t s) {
     int prof = h->dense_coop > 1;
     static const int chol_warp = getenv("BAX_CHOL_WARP") ? atoi(getenv("BAX_CHOL_WARP")) : 1;   // 0: the 256-thread diagonal-block factorisation
     int cw = chol_warp;
-    void* args[] = {(void*)&schur, (void*)&R, (void*)&lin, (void*)&nn, (void*)&B, (void*)&alpha, (void*)&ws, (void*)&coef, (void*)&prof, (void*)&cw};
+    void* args[] = {(void*)&schur, (void*)&R, (void*)&lin, (void*)&nn, (void*)&B, (void*)&alpha, (void*)&ws, (void*)&coef, (void*)&prof, (void*)&cw, (void*)&step};
     BaxTimer t(h, BAX_T_DENSE, s, 1);
     BAX_CUDA(cudaLaunchCooperativeKernel((void*)k_dense_solve1_coop, dim3(G), dim3(CG_THREADS), args, sm, s));
     return BAX_OK;
@@ -641,11 +649,11 @@ int bax_dense_solve1(bax_handle* h, cudaStream_t s) {
   static const int small_nt = getenv("BAX_DENSE_SMALL_NT") ? atoi(getenv("BAX_DENSE_SMALL_NT")) : 256;   // tuning aid: 1024 = one instance for all
   if (n <= 96 && small_nt == 256) {
     BAX_CUDA(cudaFuncSetAttribute(k_dense_solve1<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    k_dense_solve1<256><<<1, 256, sm, s>>>(h->buf[BAX_BUF_SCHUR], h->R, h->buf[BAX_BUF_LIN], n, h->B, h->alpha, h->dense_ws, h->coef);
+    k_dense_solve1<256><<<1, 256, sm, s>>>(h->buf[BAX_BUF_SCHUR], h->R, h->buf[BAX_BUF_LIN], n, h->B, h->alpha, h->dense_ws, h->coef, step);
   } else {
     BAX_CUDA(cudaFuncSetAttribute(k_dense_solve1<DN_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
     k_dense_solve1<DN_THREADS><<<1, DN_THREADS, sm, s>>>(h->buf[BAX_BUF_SCHUR], h->R, h->buf[BAX_BUF_LIN], n, h->B, h->alpha,
-                                                         h->dense_ws, h->coef);
+                                                         h->dense_ws, h->coef, step);
   }
   BAX_LAUNCH_CHECK();
   return BAX_OK;

@@ -78,6 +78,7 @@ struct bax_handle {
   double* syrk_part;         // split-K partial tiles
   size_t syrk_part_bytes;
   double* lin_part;          // per-chunk camera sums of k_lin_fused [chunks][C][28]
+  int lin_staged;            // k_gp_bone's last block already gathered the scalars bax_linearize_finish reads back
   unsigned* tickets;         // [16] arrival counters of the kernels that fold their own partials (zero between launches)
   size_t lin_part_bytes;
   double* dense_ws;          // S factor (6C x 6C), Z (B x 6C), LT (B x B), pc, w, misc
@@ -305,7 +306,7 @@ int bax_syrk(bax_handle* h, const double* X, int rows, int64_t K, int64_t ldx, d
              cudaStream_t s);
 int bax_syrk_aug(bax_handle* h, const double* X, int rows, int ne, int64_t K, int64_t ldx, double* out /*[rows+ne][ldo]*/, int ldo,
                  cudaStream_t s);
-int bax_dense_solve1(bax_handle* h, cudaStream_t s);
+int bax_dense_solve1(bax_handle* h, double* step, cudaStream_t s);
 int bax_dense_solve2(bax_handle* h, cudaStream_t s);
 int bax_scatter_cam_step(bax_handle* h, double* step, cudaStream_t s);
 int bax_bone_pass1(bax_handle* h, const double* theta, cudaStream_t s);

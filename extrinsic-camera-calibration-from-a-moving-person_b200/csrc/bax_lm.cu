@@ -315,7 +315,8 @@ template <int R>
 __global__ void __launch_bounds__(128, 4)
 k_lin_fused(const double* __restrict__ campack, const double* __restrict__ x, const double2* __restrict__ y,
             const double* __restrict__ s, int64_t P, int C, double* __restrict__ Vp, double* __restrict__ gp,
-            double* __restrict__ part /*[gridDim.x][C][28]*/) {
+            double* __restrict__ part /*[gridDim.x][C][28]*/, double* __restrict__ camsum /*[C][28]*/,
+            unsigned* __restrict__ ticket /*null: the caller reduces `part` with a kernel of its own*/) {
   extern __shared__ __align__(16) double smf[];  // cams [C][CAMPACK] | X [4][8 LCM_LD] | red [2][4][64]
   double* cams = smf;
   double* Xall = smf + C * CAMPACK;
@@ -402,6 +403,15 @@ k_lin_fused(const double* __restrict__ campack, const double* __restrict__ x, co
 #pragma unroll
     for (int k = 0; k < 3; ++k) gp[3 * pt[r] + k] = g[r][k];
   }
+  // small problems: the block that finishes last adds the chunks up, one value per thread, chunks in order
+  if (ticket && bax_last_block(ticket)) {
+    const int nv = C * 28;
+    for (int v = threadIdx.x; v < nv; v += 128) {
+      double acc = 0.0;
+      for (unsigned b = 0; b < gridDim.x; ++b) acc += __ldcg(part + (size_t)b * nv + v);
+      camsum[v] = acc;
+    }
+  }
 }
 
 // scatter the per-camera sums and the orientation-row SYRK into the packed LIN buffer
@@ -458,12 +468,24 @@ __device__ __forceinline__ void bone_u(const double* __restrict__ x, int64_t fra
 // g_p += sum_b u_pb r_b; partial sums of |g_p|^2, |x_p|^2 and max |g_p|.
 __global__ void __launch_bounds__(256)
 k_gp_bone(const double* __restrict__ x, int64_t P, int J, const int32_t* __restrict__ bones,
-          const int32_t* __restrict__ joint_bones, const double* __restrict__ Lbar, const double* __restrict__ rb,
+          const int32_t* __restrict__ joint_bones, const double* __restrict__ bone_buf /*[B] sums, [B] count*/,
+          const double* __restrict__ ssq /*[B]*/, int B, double lam2, double* __restrict__ Lbar_out, double* __restrict__ rb_out,
           double scale, double* __restrict__ gp, const double* __restrict__ Vp,
           double* __restrict__ part /*[grid][2]*/, double* __restrict__ pmax /*[2][grid]*/,
-          double* __restrict__ norm_out /*[2]*/, double* __restrict__ gmax_out /*[2]*/, unsigned* __restrict__ ticket) {
+          double* __restrict__ norm_out /*[2]*/, double* __restrict__ gmax_out /*[2]*/, unsigned* __restrict__ ticket,
+          const double* __restrict__ stage_lin_tail /*null: no staging*/, const double* __restrict__ stage_theta, int C6,
+          double* __restrict__ stage_out) {
   __shared__ double sm[2 * 32];
   __shared__ double smax[16];
+  // Lbar_b and r_b = lam2 ssq_b / Ntot (was: k_bone_finalize before this kernel); block 0 publishes them
+  __shared__ double Lbar[BAX_MAX_B], rb[BAX_MAX_B];
+  if (threadIdx.x < BAX_MAX_B) {
+    const int b = threadIdx.x;
+    const double lb = b < B ? bone_buf[b] / bone_buf[B] : 0.0, r = b < B ? lam2 * ssq[b] / bone_buf[B] : 0.0;
+    Lbar[b] = lb; rb[b] = r;
+    if (blockIdx.x == 0 && b < B) { Lbar_out[b] = lb; rb_out[b] = r; }
+  }
+  __syncthreads();
   double acc[2] = {0, 0}, mx = 0, mv = 0;
   for (int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x; p < P; p += (int64_t)gridDim.x * 256) {
     int j = (int)(p % J); int64_t fb = (p - j) * 3;
@@ -499,6 +521,15 @@ k_gp_bone(const double* __restrict__ x, int64_t P, int J, const int32_t* __restr
     bax_fold_sum<256>(part, gridDim.x, 2, norm_out, sm);
     bax_fold_max<256>(pmax, gridDim.x, gmax_out, sm);
     bax_fold_max<256>(pmax + gridDim.x, gridDim.x, gmax_out + 1, sm);
+    if (stage_lin_tail) {                        // was: k_lin_stage (runs only when nothing is all-reduced in between)
+      const int n1 = C6 + B + 2;
+      for (int i = threadIdx.x; i < n1; i += blockDim.x) stage_out[i] = stage_lin_tail[i];
+      for (int i = threadIdx.x; i < C6; i += blockDim.x) stage_out[n1 + 6 + i] = stage_theta[i];
+      if (threadIdx.x == 0) {
+        stage_out[n1] = norm_out[0]; stage_out[n1 + 1] = norm_out[1]; stage_out[n1 + 2] = gmax_out[0];
+        stage_out[n1 + 3] = bone_buf[B]; stage_out[n1 + 4] = gmax_out[1]; stage_out[n1 + 5] = 0.0;
+      }
+    }
   }
 }
 __global__ void k_reduce_max(const double* __restrict__ v, int n, double* __restrict__ out) {
@@ -548,6 +579,7 @@ extern "C" int bax_linearize_mid(bax_handle* h, void* stream) {
     // 0..3 = DFMA camera kernel at 256x1, 128x3, 256x2, 128x4 CTAs/SM + k_lin_pt
     static const int lc_variant = getenv("BAX_LINCAM") ? atoi(getenv("BAX_LINCAM")) : 5;
     double* camsum = h->partials + (1 << 20);    // [C][28]
+    bool lin_fold = false;
     const int nbp = (int)((h->P + 127) / 128);
     if (lc_variant >= 5) {
       // one round of 128 points per CTA: two rounds (half the partials, 18 more accumulator registers) measured
@@ -562,9 +594,12 @@ extern "C" int bax_linearize_mid(bax_handle* h, void* stream) {
       }
       const size_t smem = sizeof(double) * ((size_t)C * CAMPACK + 4 * 8 * LCM_LD + 2 * 256);
       BAX_CUDA(cudaFuncSetAttribute(k_lin_fused<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      k_lin_fused<1><<<g, 128, smem, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, h->Vp, h->gp, h->lin_part);
+      const bool fold = (size_t)g * C * 28 <= 32768;             // a 4-camera problem: one launch fewer
+      k_lin_fused<1><<<g, 128, smem, s>>>(h->campack_lin, x, (const double2*)h->y2d, h->s2d, h->P, C, h->Vp, h->gp, h->lin_part,
+                                          camsum, fold ? h->tickets + 4 : nullptr);
       BAX_LAUNCH_CHECK();
-      rc = bax_reduce_partials(h, h->lin_part, g, C * 28, camsum, s); if (rc) return rc;
+      if (!fold) { rc = bax_reduce_partials(h, h->lin_part, g, C * 28, camsum, s); if (rc) return rc; }
+      lin_fold = fold;
     } else {
       int g = obs_grid(h);
       double* part = h->partials;                  // [g][C][28]
@@ -584,7 +619,7 @@ extern "C" int bax_linearize_mid(bax_handle* h, void* stream) {
       BAX_LAUNCH_CHECK();
     }
     rc = bax_bone_pass2(h, h->theta_lin, lin + (size_t)C6 * C6 + C6, s); if (rc) return rc;
-    t.nl = (lc_variant >= 5 ? 2 : 3) + (h->B > 0 ? 1 : 0);
+    t.nl = (lc_variant >= 5 ? (lin_fold ? 1 : 2) : 3) + (h->B > 0 ? 1 : 0);
   }
   double* v3d = nullptr;
   if (h->Nv > 0) {
@@ -607,17 +642,22 @@ extern "C" int bax_linearize_mid(bax_handle* h, void* stream) {
 extern "C" int bax_linearize_post(bax_handle* h, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
   const int C6 = 6 * h->C;
-  BaxTimer t(h, BAX_T_LIN, s, 2);
+  BaxTimer t(h, BAX_T_LIN, s, 1);
   double* lin = h->buf[BAX_BUF_LIN];
-  k_bone_finalize<<<1, 32, 0, s>>>(h->buf[BAX_BUF_BONE], lin + (size_t)C6 * C6 + C6, h->B, h->lam2, h->Lbar, h->rb);
-  BAX_LAUNCH_CHECK();
   int g = row_grid(h, h->P);
   double* part = h->partials; double* pmax = h->partials + (1 << 16);
   // scale = lam2 * 2 / Ntot ; Ntot lives on device (buf[BONE][B]); single-GPU fast path reads host N,
   // multi-GPU callers set it through bax_set_global_frames before linearising.
   double scale = h->lam2 * 2.0 / (double)h->n_frames_global;
-  k_gp_bone<<<g, 256, 0, s>>>(h->theta_lin + C6, h->P, h->J, h->bones, h->joint_bones, h->Lbar, h->rb, scale, h->gp, h->Vp, part, pmax,
-                              h->buf[BAX_BUF_NORM], h->buf[BAX_BUF_GMAX], h->tickets + 2);
+  // an unsharded problem (no communicator attached, all frames local: frame-sharded callers, whichever language issues
+  // their collectives, announce the global frame count through bax_set_global_frames) has nothing all-reduced between
+  // this kernel and bax_linearize_finish: the last block gathers the scalars for the read-back as well, and
+  // h->lin_staged tells bax_linearize_finish to skip k_lin_stage
+  h->lin_staged = h->comm == nullptr && h->n_frames_global == (int64_t)h->N;
+  k_gp_bone<<<g, 256, 0, s>>>(h->theta_lin + C6, h->P, h->J, h->bones, h->joint_bones, h->buf[BAX_BUF_BONE], lin + (size_t)C6 * C6 + C6,
+                              h->B, h->lam2, h->Lbar, h->rb, scale, h->gp, h->Vp, part, pmax,
+                              h->buf[BAX_BUF_NORM], h->buf[BAX_BUF_GMAX], h->tickets + 2,
+                              h->lin_staged ? lin + (size_t)C6 * C6 : nullptr, h->theta_lin, C6, h->lin_stage);
   BAX_LAUNCH_CHECK();
   return BAX_OK;
 }
@@ -643,10 +683,13 @@ extern "C" int bax_linearize_finish(bax_handle* h, double* out_host, void* strea
   // separate driver round trip: ~40 us per linearisation, which a 4-camera problem feels)
   const int n_stage = C6 + B + 8 + C6;
   double* lin = h->buf[BAX_BUF_LIN];
-  k_lin_stage<<<1, 256, 0, s>>>(lin + (size_t)C6 * C6, h->buf[BAX_BUF_NORM], h->buf[BAX_BUF_GMAX], h->buf[BAX_BUF_BONE] + B,
-                                h->theta_lin, C6, B, h->lin_stage);
-  BAX_LAUNCH_CHECK();
-  h->t_launch[BAX_T_LIN] += 1;
+  if (!h->lin_staged) {
+    k_lin_stage<<<1, 256, 0, s>>>(lin + (size_t)C6 * C6, h->buf[BAX_BUF_NORM], h->buf[BAX_BUF_GMAX], h->buf[BAX_BUF_BONE] + B,
+                                  h->theta_lin, C6, B, h->lin_stage);
+    BAX_LAUNCH_CHECK();
+    h->t_launch[BAX_T_LIN] += 1;
+  }
+  h->lin_staged = 0;
   double* stage = h->host_pinned + 64;
   BAX_CUDA(cudaMemcpyAsync(stage, h->lin_stage, sizeof(double) * n_stage, cudaMemcpyDeviceToHost, s));
   BAX_CUDA(bax_stream_wait(h, s));

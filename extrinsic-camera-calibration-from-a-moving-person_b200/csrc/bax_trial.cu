@@ -217,11 +217,9 @@ extern "C" int bax_trial_mid(bax_handle* h, double* step, int need_phi_prime, vo
   if (!h || !h->Yhat || !step) { bax_set_error("bax_trial_mid: bad argument"); return BAX_E_ARG; }
   cudaStream_t s = (cudaStream_t)stream;
   const int C = h->C, C6 = 6 * C, B = h->B;
-  int rc = bax_dense_solve1(h, s); if (rc) return rc;
+  int rc = bax_dense_solve1(h, step, s); if (rc) return rc;      // camera part of the step included
   {
-    BaxTimer t(h, BAX_T_BACKSUB, s, 2);
-    // camera part of the step, theta order (rvecs first, then tvecs): done by a tiny copy kernel in bax_dense.cu
-    rc = bax_scatter_cam_step(h, step, s); if (rc) return rc;
+    BaxTimer t(h, BAX_T_BACKSUB, s, 1);
     int nb = (int)((h->P + 127) / 128);
     size_t sm = sizeof(double) * (((C6 + B + 1) & ~1) + 3 * 32);
     double* part = h->partials;
