@@ -11,6 +11,8 @@ SIGS = {
     "rsx_sample_stream": (i32, [P_u64, i64, i64, i64, P_i32, P_i32]),
     "rsx_problem_set": (i32, [vp, i32, i64, i64, vp, vp, vp]),
     "rsx_fit_score": (i32, [vp, vp, vp, i64, vp, vp, vp, vp]),
+    "rsx_prune": (i32, [vp, i32, vp]),
+    "rsx_prune_stats": (i32, [vp, P_i64, P_f64, vp]),
     "rsx_argmin": (i32, [vp, vp, i64, P_i64, P_f64, vp]),
     "rsx_argmin_static": (i32, [i32, vp, i64, vp, vp]),
     "rsx_winner_masks": (i32, [vp, vp, vp, f64, f64, vp, vp, vp, vp, P_i64, vp]),

@@ -138,6 +138,75 @@ k_rsx_score(int C, int64_t N, int64_t M, const double* __restrict__ v, const dou
   }
 }
 
+// Scoring with an exact bail-out (rsx_prune).  RANSAC only keeps the hypothesis with the smallest score, and the score
+// sqrt(sum_rays e^2) / M + sqrt(sum_dirs ang^2) / N only grows while rays are added.  So a CTA first forms the (cheap)
+// direction term, then walks the rays in pieces of PRUNE_RAYS per thread and after each piece compares the lower bound
+// sqrt(partial) / M + direction term with the best complete score any CTA has published so far (atomicMin on the bits of
+// a positive double, fit_stats[5]); a hypothesis whose bound is already LARGER than that cannot be the first minimum and
+// is dropped (score = +inf, counted in fit_stats[6]).  Ties are never dropped (strict '>'), NaN sums never compare
+// true, and a hypothesis that survives accumulates exactly the sequence k_rsx_score<1> accumulates: the winner, its
+// score and everything derived from it are bit-identical to the unpruned pass; which losers are cut short depends on
+// timing.  (The reference scores every hypothesis in full, calib_ransac.py:154-181; its result depends on the minimum only.)
+#define PRUNE_RAYS 2                             // measured per 100 k hypotheses: 1 -> 29.0 ms, 2 -> 29.7, 4 -> 31.4, 8 -> 34.8 (the whole call; 78 unpruned)
+template <int MINB>
+__global__ void __launch_bounds__(SCORE_THREADS, MINB)
+k_rsx_score_prune(int C, int64_t N, int64_t M, const double* __restrict__ v, const double* __restrict__ n,
+                  const double* __restrict__ Rt, int64_t H, double* __restrict__ score,
+                  const uint8_t* __restrict__ skip, const int32_t* __restrict__ list, const unsigned long long* __restrict__ n_list,
+                  unsigned long long* __restrict__ best_bits, unsigned long long* __restrict__ pruned) {
+  extern __shared__ __align__(16) double sm[];       // [C][12] model, 2*32 reduction scratch, [C][9] R_0 R_c^T
+  double* sRt = sm;
+  double* red = sm + ((12 * C + 1) & ~1);
+  double* sG = red + 64;
+  __shared__ double s_dirs; __shared__ int s_bail;
+  CtaCtx g{(int)threadIdx.x, (int)blockDim.x};
+  const int64_t count = list ? (int64_t)*n_list : H;
+  const int64_t piece = (int64_t)PRUNE_RAYS * blockDim.x;
+  for (int64_t it = blockIdx.x; it < count; it += gridDim.x) {
+    const int64_t h = list ? (int64_t)list[it] : it;
+    if (skip && skip[h]) continue;                       // uniform over the CTA
+    __syncthreads();
+    for (int i = threadIdx.x; i < 12 * C; i += blockDim.x) sRt[i] = Rt[(size_t)h * C * 12 + i];
+    __syncthreads();
+    score_dirs_prepare(g, C, sRt, sG);
+    __syncthreads();
+    double a1[1] = {score_dirs_sum(g, C, N, v, sG)};
+    block_sum<1>(a1, red);
+    if (threadIdx.x == 0) { s_dirs = a1[0]; s_bail = 0; }
+    __syncthreads();
+    const double dirs_total = s_dirs, dirs_term = sqrt(dirs_total) / (double)N;
+    double acc0 = 0.0;
+    bool bail = false;
+    for (int64_t i0 = 0; i0 < M; i0 += piece) {
+      const int64_t i1 = i0 + piece < M ? i0 + piece : M;
+      score_points_accum<1>(g, C, M, n, sRt, i0, i1, acc0);
+      if (i1 < M) {
+        double p[1] = {acc0};
+        block_sum<1>(p, red);                            // ends with the value in thread 0; barriers inside
+        if (threadIdx.x == 0) {
+          const double lb = sqrt(p[0]) / (double)M + dirs_term;
+          const double best = __longlong_as_double((long long)*(volatile unsigned long long*)best_bits);
+          s_bail = lb > best ? 1 : 0;
+        }
+        __syncthreads();
+        bail = s_bail != 0;
+        if (bail) break;
+      }
+    }
+    if (bail) {
+      if (threadIdx.x == 0) { score[h] = INFINITY; atomicAdd(pruned, 1ULL); }
+      continue;
+    }
+    double a0[1] = {acc0};
+    block_sum<1>(a0, red);
+    if (threadIdx.x == 0) {
+      const double sc = sqrt(a0[0]) / (double)M + sqrt(dirs_total) / (double)N;      // calib_ransac.py:179-181
+      score[h] = sc;
+      if (sc >= 0.0) atomicMin(best_bits, (unsigned long long)__double_as_longlong(sc));   // NaN: not published
+    }
+  }
+}
+
 // first minimum under strict '<' starting from +inf (calib_ransac.py:139,182): NaN / +inf never win
 __global__ void __launch_bounds__(1024)
 k_rsx_argmin(const double* __restrict__ score, int64_t H, double* __restrict__ out /*[2]: index, score*/) {
@@ -418,7 +487,10 @@ extern "C" int rsx_fit_score(rsx_handle* h, const int32_t* samp_v, const int32_t
     RsxTimer t(h, RSX_T_SCORE, s, pending ? 2 : 1);
     const uint8_t* skip = pending ? h->deferred_flag : nullptr;
     auto launch = [&](const uint8_t* sk, const int32_t* list, const unsigned long long* nl, int64_t g) {
-      if (h->score_mode == 0)
+      if (h->prune && h->score_mode == 1 && !parts)
+        k_rsx_score_prune<3><<<(unsigned)g, SCORE_THREADS, smem, s>>>(h->C, h->N, h->M, h->v, h->n, models, H, score, sk, list, nl,
+                                                                       (unsigned long long*)h->fit_stats + 5, (unsigned long long*)h->fit_stats + 6);
+      else if (h->score_mode == 0)
         k_rsx_score<0, 3><<<(unsigned)g, SCORE_THREADS, smem, s>>>(h->C, h->N, h->M, h->v, h->n, models, H, score, parts, sk, list, nl);
       else if (h->score_mode == 2)
         k_rsx_score<1, 2><<<(unsigned)g, SCORE_THREADS, smem, s>>>(h->C, h->N, h->M, h->v, h->n, models, H, score, parts, sk, list, nl);
@@ -433,6 +505,30 @@ extern "C" int rsx_fit_score(rsx_handle* h, const int32_t* samp_v, const int32_t
       BAX_LAUNCH_CHECK();
     }
   }
+  return BAX_OK;
+}
+
+// Bail-out scoring on / off (see k_rsx_score_prune); every call resets the running bound and the count.
+extern "C" int rsx_prune(rsx_handle* h, int on, void* stream) {
+  if (!h) { bax_set_error("rsx_prune: null handle"); return BAX_E_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  BAX_CUDA(cudaSetDevice(h->device));
+  h->prune = on ? 1 : 0;
+  static const unsigned long long init[2] = {0x7ff0000000000000ULL /* +inf */, 0ULL};
+  BAX_CUDA(cudaMemcpyAsync((unsigned long long*)h->fit_stats + 5, init, sizeof(init), cudaMemcpyHostToDevice, s));
+  return BAX_OK;
+}
+// out_host[0..1] = { hypotheses dropped by the bail-out since the last rsx_prune, the best complete score published so
+// far (+inf if none) }.  Synchronises.
+extern "C" int rsx_prune_stats(rsx_handle* h, int64_t* pruned_host, double* best_host, void* stream) {
+  if (!h || !pruned_host) { bax_set_error("rsx_prune_stats: bad argument"); return BAX_E_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  BAX_CUDA(cudaSetDevice(h->device));
+  unsigned long long v[2];
+  BAX_CUDA(cudaMemcpyAsync(v, (unsigned long long*)h->fit_stats + 5, sizeof(v), cudaMemcpyDeviceToHost, s));
+  BAX_CUDA(cudaStreamSynchronize(s));
+  pruned_host[0] = (int64_t)v[1];
+  if (best_host) memcpy(best_host, &v[0], sizeof(double));
   return BAX_OK;
 }
 

@@ -381,10 +381,12 @@ __host__ __device__ inline void score_ray_sum(int C, int64_t M, const double* __
 }
 
 //   MODE 1 (default): Rayleigh-quotient eigen-solver + common-denominator sum; MODE 0: round-1 arithmetic
+//   rays i0 + tid, i0 + tid + nt, ... < i1 of this thread added to acc (score_points_sum = the range [0, M); the
+//   pruned score kernel walks the same sequence in pieces, so both give the same bits)
 template <int MODE, class G>
-__host__ __device__ inline double score_points_sum(const G& g, int C, int64_t M, const double* __restrict__ n, const double* Rt) {
-  double acc = 0.0;
-  for (int64_t i = g.tid; i < M; i += g.nt) {
+__host__ __device__ inline void score_points_accum(const G& g, int C, int64_t M, const double* __restrict__ n, const double* Rt,
+                                                   int64_t i0, int64_t i1, double& acc) {
+  for (int64_t i = i0 + g.tid; i < i1; i += g.nt) {
     double m[10];
 #pragma unroll
     for (int e = 0; e < 10; ++e) m[e] = 0.0;
@@ -401,6 +403,11 @@ __host__ __device__ inline double score_points_sum(const G& g, int C, int64_t M,
       score_ray(C, M, n, Rt, i, X, nullptr, nullptr, 0.0, nullptr, acc);
     }
   }
+}
+template <int MODE, class G>
+__host__ __device__ inline double score_points_sum(const G& g, int C, int64_t M, const double* __restrict__ n, const double* Rt) {
+  double acc = 0.0;
+  score_points_accum<MODE>(g, C, M, n, Rt, 0, M, acc);
   return acc;
 }
 

@@ -15,6 +15,7 @@ struct rsx_handle {
   double* fit_scratch;  // global H/V workspace when 3(10+C) is too large for shared memory
   size_t fit_scratch_bytes;
   int fit_mode;         // 1: warp-per-hypothesis arrow solver where it fits, Jacobi fall-backs in a second pass (env RSX_FIT_MODE=0: CTA Jacobi kernel; 2: fall-backs inline)
+  int prune;            // rsx_prune: exact bail-out in the score pass (fit_stats[5] = bits of the best complete score, [6] = dropped)
   int score_mode;       // 1: Rayleigh-quotient DLT eigen-solver + common-denominator error sum (env RSX_SCORE_MODE=0: round-1 arithmetic)
   void* fit_stats;      // device [8] uint64: Jacobi fall-backs, total sweeps of the arrow solver, work counter of k_rsx_fit_warp, deferred fits of this launch, deferred fits in total
   double last_eigs[6];  // Ritz values of the 6 smallest eigenpairs of the last rsx_calib_linear (ascending)

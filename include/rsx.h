@@ -44,6 +44,17 @@ int rsx_problem_set(rsx_handle* h, int C, int64_t N, int64_t M, const double* v,
 int rsx_fit_score(rsx_handle* h, const int32_t* samp_v, const int32_t* samp_m, int64_t H, double* score,
                   double* Rt, double* parts, void* stream);
 
+/* Exact bail-out in the score pass of rsx_fit_score (no counterpart in the reference, which scores every hypothesis in
+ * full at calib_ransac.py:154-181 and then keeps the minimum, :182-189).  The score only grows while rays are added, so
+ * a hypothesis whose partial score already exceeds the best complete score published so far cannot be the first minimum:
+ * it is dropped and reported as +inf.  The winner, its score and every output derived from it are bit-identical to the
+ * unpruned pass; WHICH losers are cut short depends on timing.  on = 1 / 0; every call resets the running bound and the
+ * count (call it once per RANSAC run; the bound then carries over the chunks of that run).  Ignored when rsx_fit_score
+ * is asked for `parts`.  rsx_prune_stats: hypotheses dropped since the last rsx_prune and the best complete score so far
+ * (+inf if none); synchronises. */
+int rsx_prune(rsx_handle* h, int on, void* stream);
+int rsx_prune_stats(rsx_handle* h, int64_t* pruned_host, double* best_host, void* stream);
+
 /* First minimum of score[0..H) (strict '<' from +inf: NaN and +inf never win, calib_ransac.py:182).
  * best_host[0] = index or -1, score_host[0] = its score. Synchronises. */
 int rsx_argmin(rsx_handle* h, const double* score, int64_t H, int64_t* best_host, double* score_host, void* stream);

@@ -245,3 +245,66 @@ def test_calib_linear_eigenvalues_and_warning(golden_dir, capsys):
     cl.calib_linear(v, n)
     out = capsys.readouterr().out
     assert ("WARN: degenerate case" in out) == bool(w[3] / w[4] > 1e-4)
+
+
+@pytest.mark.parametrize("case", ["c4", "c3", "c4_long"])
+def test_pruned_scoring_keeps_the_winner_and_every_surviving_score(golden_dir, case):
+    """rsx_prune: the exact bail-out may only drop hypotheses that cannot be the first minimum.  Against the unpruned
+    pass on the same hypotheses: same winner, winner's score and every surviving score bit for bit, every dropped
+    hypothesis strictly worse than the winner; the drop-in returns the same winner, masks and final model."""
+    g = np.load(os.path.join(golden_dir, f"ransac_{case}.npz"))
+    prob = cr.RansacProblem(g["vc"], g["n"])
+    sn, sm = g["sn"].astype(np.int32), g["sm"].astype(np.int32)
+    exact = prob.fit_score(sn, sm).cpu().numpy()
+    b = int(np.nanargmin(exact))
+    assert b == int(g["best"])
+    for _ in range(2):                                     # twice: the bound must be reset by each rsx_prune call
+        prob.prune(True)
+        pruned = prob.fit_score(sn, sm).cpu().numpy()
+        n_pruned, best = prob.prune_stats()
+        prob.prune(False)
+        kept = ~(np.isposinf(pruned) & ~np.isposinf(exact))       # dropped = +inf where the full pass has a number (or NaN)
+        assert kept[b] and pruned[b] == exact[b] and best == exact[b]
+        assert int(np.nanargmin(pruned)) == b
+        assert np.array_equal(pruned[kept], exact[kept], equal_nan=True)
+        assert np.all(exact[~kept] > exact[b]) and n_pruned == int(np.count_nonzero(~kept))
+    # (the golden scenes have 325 rays: fewer than one piece of the bail-out, so nothing is dropped here; the scene
+    # below is large enough)
+    assert np.array_equal(prob.fit_score(sn, sm).cpu().numpy(), exact)      # switched off again: the full pass
+    out0, i0 = cr.calib_linear_ransac(g["vc"], g["n"], g["K"], int(g["n_iter"]), float(g["th_2d"]), float(g["th_3d"]),
+                                      int(g["seed"]), return_info=True, verbose=False, prob=prob, prune=False)
+    out1, i1 = cr.calib_linear_ransac(g["vc"], g["n"], g["K"], int(g["n_iter"]), float(g["th_2d"]), float(g["th_3d"]),
+                                      int(g["seed"]), return_info=True, verbose=False, prob=prob, prune=True)
+    assert i0["best"] == i1["best"] == int(g["best"]) and i0["best_score"] == i1["best_score"]
+    assert np.array_equal(i0["mask_2d"], i1["mask_2d"]) and np.array_equal(i0["mask_3d"], i1["mask_3d"])
+    assert np.array_equal(out0[0], out1[0]) and np.array_equal(out0[1], out1[1])
+    assert i0["pruned"] == 0
+    prob.close()
+
+
+def test_pruned_scoring_drops_losers_on_a_larger_scene():
+    """200 frames (3000 rays, 2400 directions), 3000 hypotheses: the bail-out really drops hypotheses, and what it keeps
+    and returns is what the full pass gives."""
+    sc = scene.cfg1(seed=2000, N=200)
+    v, n = cr.ransac_inputs(sc.p3d, sc.s3d, sc.p2d, sc.s2d, sc.K, OP_BONE)
+    prob = cr.RansacProblem(v, n)
+    plan = cr.SamplePlan.get(prob.N, prob.M, 5, 3000)
+    plan.ensure(3000)
+    sn, sm = plan.sn[:3000], plan.sm[:3000]
+    exact = prob.fit_score(sn, sm).cpu().numpy()
+    b = int(np.nanargmin(exact))
+    prob.prune(True)
+    pruned = prob.fit_score(sn, sm).cpu().numpy()
+    n_pruned, best = prob.prune_stats()
+    prob.prune(False)
+    kept = ~(np.isposinf(pruned) & ~np.isposinf(exact))           # degenerate samples score NaN in both passes
+    assert n_pruned > 100 and n_pruned == int(np.count_nonzero(~kept))
+    assert kept[b] and int(np.nanargmin(pruned)) == b and pruned[b] == exact[b] == best
+    assert np.array_equal(pruned[kept], exact[kept], equal_nan=True) and np.all(exact[~kept] > exact[b])
+    th2d, th3d = 50.0, 5.0 / 180 * np.pi
+    out0, i0 = cr.calib_linear_ransac(v, n, sc.K, 3000, th2d, th3d, 5, return_info=True, verbose=False, prob=prob, prune=False)
+    out1, i1 = cr.calib_linear_ransac(v, n, sc.K, 3000, th2d, th3d, 5, return_info=True, verbose=False, prob=prob, prune=True)
+    assert i0["best"] == i1["best"] == b and i1["pruned"] > 100
+    assert np.array_equal(i0["mask_2d"], i1["mask_2d"]) and np.array_equal(i0["mask_3d"], i1["mask_3d"])
+    assert np.array_equal(out0[0], out1[0]) and np.array_equal(out0[1], out1[1])
+    prob.close()
