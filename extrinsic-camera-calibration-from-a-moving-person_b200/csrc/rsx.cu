@@ -147,6 +147,8 @@ k_rsx_score(int C, int64_t N, int64_t M, const double* __restrict__ v, const dou
 // true, and a hypothesis that survives accumulates exactly the sequence k_rsx_score<1> accumulates: the winner, its
 // score and everything derived from it are bit-identical to the unpruned pass; which losers are cut short depends on
 // timing.  (The reference scores every hypothesis in full, calib_ransac.py:154-181; its result depends on the minimum only.)
+// Measured and not kept: walking the directions piecewise alongside the rays instead of first — the bound is weaker while
+// the direction term is incomplete: 33.5 against 29.7 ms per 100 k hypotheses.
 #define PRUNE_RAYS 2                             // measured per 100 k hypotheses: 1 -> 29.0 ms, 2 -> 29.7, 4 -> 31.4, 8 -> 34.8 (the whole call; 78 unpruned)
 template <int MINB>
 __global__ void __launch_bounds__(SCORE_THREADS, MINB)
