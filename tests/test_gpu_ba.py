@@ -310,11 +310,11 @@ def test_rejected_step_restores_linearisation(golden_dir):
     assert torch.equal(prob.step, p0)
 
 
-@pytest.mark.parametrize("C,N", [(9, 60), (11, 40), (16, 30), (33, 20)])
+@pytest.mark.parametrize("C,N", [(9, 60), (11, 40), (16, 30), (33, 20), (70, 6)])
 def test_damped_step_many_cameras(C, N):
-    """Reduced systems of 54..198 unknowns: DMMA SYRK tiles with the trailing rows fused into diagonal tiles (one and
-    several tile rows) and the cooperative multi-CTA reduced solve, against a dense solve of the oracle's normal
-    equations."""
+    """Reduced systems of 54..420 unknowns: DMMA SYRK tiles with the trailing rows fused into diagonal tiles (one to
+    five tile rows, i.e. up to ten off-diagonal tiles and the per-kind K cut) and the cooperative multi-CTA reduced
+    solve, against a dense solve of the oracle's normal equations."""
     sc = scene.make_scene(C=C, N=N, seed=300 + C, score_mode="uniform", p_drop_2d=0.2, p_drop_3d=0.1)
     sp2d, ss2d, sp3d, ss3d = scene.ba_inputs(sc)
     J = ss2d.shape[2]
